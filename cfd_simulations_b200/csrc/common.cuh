@@ -1,0 +1,117 @@
+// common.cuh — shared device helpers for libb200cfd (sm_100a).
+// Layout: row-major (ny, nx) with row pitch `pitch` (elements), x fastest.  i = row (y), j = column (x).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+namespace b200cfd {
+
+// Geometry + precomputed coefficients (host-computed in double with the reference's expressions so
+// the constants are bit-identical to the oracle's: v5.py:131-132,168-169,182-183,205-210).
+struct Geom {
+    int ny, nx;          // local array shape
+    long long pitch;     // row stride in elements
+    int jg0, nxg;        // global column of local column 0, global nx (x-slab decomposition)
+    double dx, dy;
+    double hdx, hdy;     // 0.5/dx, 0.5/dy            (divergence / gradient / SUPG dx_inv)
+    double qdx, qdy;     // 0.5*hdx, 0.5*hdy          (SUPG first derivative, v5.py:137-138)
+    double hdx2, hdy2;   // hdx*hdx, hdy*hdy          (SUPG second derivative, v5.py:141-142)
+    double ax, ay;       // 1/(dx*dx), 1/(dy*dy)
+    double dinv;         // 1/(2(ax+ay))
+    double rdx, rdy;     // 1/dx, 1/dy                (upwind)
+    double hmin;         // min(dx,dy)
+    double two_dx, two_dy; // 2*dx, 2*dy              (vorticity, v5.py:369-370)
+};
+
+// Device-resident per-step control block: nothing on the host is needed between steps.
+struct StepCtl {
+    double dt;            // this step's dt (adaptive_time_step, v5.py:316-326)
+    double fs;            // min(1, step/initial_steps)          (v5.py:406)
+    double pert_scale;    // min(1, step/1000) * 0.01            (v5.py:351)
+    double phase;         // 0.02 * step                         (v5.py:352)
+    long long step;
+    // order-preserving bit patterns of non-negative doubles (atomicMax on u64)
+    unsigned long long max_div_pre, max_grad, max_div_post, max_vort, max_u, max_v;
+    unsigned long long sum_nut_bits_unused;
+    unsigned int nonfinite;
+    unsigned int pad0;
+    // adaptive-dt inputs = post-clip maxima of the state entering the step
+    double in_max_u, in_max_v, in_mean_nut;
+    // Poisson iteration control (tolerance mode runs without host round trips)
+    unsigned long long pois_change;   // running max|dphi| of the current iteration
+    double pois_last;                 // max|dphi| of the last finished iteration
+    int pois_iters;                   // iterations finished
+    int pois_done;                    // tolerance reached -> later launches exit immediately
+    unsigned int pois_blocks_done;    // last-block election counter
+    unsigned int pad1;
+};
+
+struct StepScalars {   // must match b200cfd_step_scalars (12 doubles)
+    double dt, max_div_pre, max_grad_phi, max_div_post, max_vorticity, mean_energy, max_abs_u, max_abs_v,
+        poisson_iters, poisson_change, nonfinite, step;
+};
+
+template <typename T> struct Rnd;
+template <> struct Rnd<double> { static __device__ __forceinline__ double r(double x) { return x; } };
+template <> struct Rnd<float>  { static __device__ __forceinline__ double r(double x) { return (double)(float)x; } };
+
+// a + s*(-c + l) evaluated in the field dtype (NumPy glue, v5.py:402-403)
+template <typename T> __device__ __forceinline__ double axpy_pred(double a, double s, double c, double l);
+template <> __device__ __forceinline__ double axpy_pred<double>(double a, double s, double c, double l) { return a + s * (-c + l); }
+template <> __device__ __forceinline__ double axpy_pred<float>(double a, double s, double c, double l) {
+    return (double)((float)a + (float)s * (-(float)c + (float)l));
+}
+// a - s*g evaluated in the field dtype (v5.py:416-417)
+template <typename T> __device__ __forceinline__ double axmy(double a, double s, double g);
+template <> __device__ __forceinline__ double axmy<double>(double a, double s, double g) { return a - s * g; }
+template <> __device__ __forceinline__ double axmy<float>(double a, double s, double g) { return (double)((float)a - (float)s * (float)g); }
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block max of a non-negative value -> one atomicMax per block (warp shuffle + smem tree).
+// NaN inputs are dropped by fmax (nanmax semantics).
+__device__ __forceinline__ void block_atomic_max(double v, unsigned long long* dst) {
+    __shared__ double s_red[32];
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    const int nw = (blockDim.x * blockDim.y + 31) >> 5;
+    v = warp_max(v);
+    __syncthreads();   // protect s_red reuse between consecutive calls
+    if ((tid & 31) == 0) s_red[tid >> 5] = v;
+    __syncthreads();
+    if (tid < 32) {
+        double w = tid < nw ? s_red[tid] : 0.0;
+        w = warp_max(w);
+        if (tid == 0 && w > 0.0) atomicMax(dst, (unsigned long long)__double_as_longlong(w));
+    }
+}
+
+// Block sum with a fixed reduction tree (deterministic for a fixed launch shape); result valid in thread 0.
+__device__ __forceinline__ double block_sum(double v) {
+    __shared__ double s_sum[32];
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+    const int nw = (blockDim.x * blockDim.y + 31) >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if ((tid & 31) == 0) s_sum[tid >> 5] = v;
+    __syncthreads();
+    double w = 0.0;
+    if (tid < 32) {
+        w = tid < nw ? s_sum[tid] : 0.0;
+        w = warp_sum(w);
+    }
+    return w;
+}
+
+__device__ __forceinline__ double bits_to_double(unsigned long long b) { return __longlong_as_double((long long)b); }
+
+}  // namespace b200cfd

@@ -1,0 +1,73 @@
+// kernels.h — host-side launchers of the CUDA kernels (one translation unit per kernel family).
+#pragma once
+#include "common.cuh"
+
+namespace b200cfd {
+
+struct Phys {
+    double nu_eff;        // nu + av in the field dtype (v5.py:388, LES off) ; base value when LES on
+    double V_inf, y_max, max_velocity;
+    double inv_cfg_dt;    // 1/cfg.dt  (Poisson RHS uses the CONFIG dt, v5.py:210,333)
+    int use_supg;
+    int pad;
+};
+
+// control: prepare ctl for `step` from in_max_u/v; close a step into the scalar ring
+struct CtlParams {
+    double cfl_target, dt_min, dt_max, dt_base, hmin, nu, av;
+    int adaptive_dt, initial_steps, is_f32, use_les;
+};
+
+// ---- unit kernels (one per reference @njit function) -------------------------------------------
+void launch_supg_tau(int dtype, const Geom& g, const void* u, const void* v, void* tau, double dt, double nu_eff,
+                     const void* nu_t, cudaStream_t s);
+void launch_convection(int dtype, const Geom& g, const void* u, const void* v, const void* phi, const void* tau,
+                       void* conv, int supg, cudaStream_t s);
+void launch_laplacian(int dtype, const Geom& g, const void* phi, void* lap, double nu_eff, const void* nu_t, cudaStream_t s);
+void launch_divergence(int dtype, const Geom& g, const void* u, const void* v, void* div, unsigned long long* max_out,
+                       cudaStream_t s);
+void launch_gradient(int dtype, const Geom& g, const void* phi, void* gx, void* gy, cudaStream_t s);
+void launch_smagorinsky(int dtype, const Geom& g, const void* u, const void* v, void* nu_t, double cs, cudaStream_t s);
+void launch_apply_bc(int dtype, const Geom& g, void* u, void* v, const double* y, double V_inf, double y_max,
+                     long long step, cudaStream_t s);
+void launch_apply_ibm(int dtype, const Geom& g, void* u, void* v, const double* ibm, double fs, cudaStream_t s);
+
+// ---- fused step kernels ------------------------------------------------------------------------
+// K1: u*, v* = IBM(BC(u + dt(-C + L)))        reads ctl->dt/fs/pert (device)   v5.py:388-407
+void launch_predictor(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
+                      void* us, void* vs, void* tau_or_null, const void* nu_t_or_null, const double* ibm,
+                      const double* y, cudaStream_t s);
+// K3: u = u* - dt grad(phi), max|grad phi|                                     v5.py:413-417
+void launch_correct(int dtype, const Geom& g, StepCtl* ctl, const void* us, const void* vs, const void* phi,
+                    void* u, void* v, cudaStream_t s);
+// K5: post-div max, BC, IBM, vorticity max, energy sum, clip, post-clip maxima  v5.py:421-438
+void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
+                     void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
+                     double* ke_partials, unsigned long long* cnt_partials, cudaStream_t s);
+int finalize_num_partials(const Geom& g);
+void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s);
+void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* ke_partials,
+                         const unsigned long long* cnt_partials, int n_partials, StepScalars* ring, int ring_cap,
+                         cudaStream_t s);
+void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s);
+void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, StepCtl* ctl, cudaStream_t s);
+
+// ---- Poisson -----------------------------------------------------------------------------------
+// one red-black colour half-sweep (global colour parity), fused max|dphi|, last block closes the iteration
+void launch_rbgs_color(int dtype, const Geom& g, void* phi, const void* div, const uint8_t* mask, double inv_dt,
+                       double omega, int color, StepCtl* ctl, double tol, int close_iteration, cudaStream_t s);
+void launch_jacobi(int dtype, const Geom& g, const void* phi_in, void* phi_out, const void* div, const uint8_t* mask,
+                   double dx2_over_dt, cudaStream_t s);
+void launch_poisson_reset(StepCtl* ctl, cudaStream_t s);
+// fused div(u*,v*) + exactly one red-black iteration from phi = 0 ("as executed"), + max|div|
+void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
+                    void* div_out, double inv_dt, StepCtl* ctl, double tol, cudaStream_t s);
+
+// ---- divergence clean-up (lexicographic GS by independent overlapped warp tiles) -----------------
+struct CleanPlan { int strip_w, tile_h, apron_h, apron_v; int n_strips, n_tiles; int j_first, j_end; };
+CleanPlan clean_plan(const Geom& g, int dtype, int n_sm);
+void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
+                        const void* psi_old /*NULL = zeros*/, void* psi_new, cudaStream_t s);
+void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s);
+
+}  // namespace b200cfd

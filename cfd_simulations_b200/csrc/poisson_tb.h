@@ -1,0 +1,16 @@
+// poisson_tb.h — temporally blocked (several sweeps per HBM pass) Poisson kernels: TMA-staged tile + halo in
+// shared memory.  Each entry runs as many of the requested sweeps as it can in full passes of depth T and
+// reports how many it did in *iters_done (the caller finishes the remainder with the one-sweep kernels).
+#pragma once
+#include "common.cuh"
+
+namespace b200cfd {
+struct PoissonTB;
+const char* poisson_tb_error();
+void poisson_tb_destroy(PoissonTB* tb);
+// returns 0 on success (possibly with *iters_done == 0 when the shape is not supported), < 0 on CUDA errors
+int poisson_tb_jacobi(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
+                      double dx2_over_dt, int sweeps, int depth, int* iters_done, cudaStream_t s);
+int poisson_tb_rbsor(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
+                     double inv_dt, double omega, int iters, int depth, int* iters_done, cudaStream_t s);
+}  // namespace b200cfd

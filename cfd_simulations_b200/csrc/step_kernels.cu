@@ -1,0 +1,561 @@
+// step_kernels.cu — momentum predictor, divergence, correction, finalize (BC + IBM + diagnostics) and the
+// device-resident step control.  Reference: python/flow_over_cylinder (Fischer)/v5.py:96-200,228-237,316-441.
+// All arithmetic is done in double after the load; values the reference materialises as arrays of the
+// field dtype are rounded to T at the same points (Rnd<T>), so fp32 storage follows the reference too.
+#include "kernels.h"
+
+namespace b200cfd {
+
+#define BX 64
+#define BY 4
+static inline dim3 grid2d(const Geom& g) { return dim3((g.nx + BX - 1) / BX, (g.ny + BY - 1) / BY); }
+static const dim3 kBlock(BX, BY);
+
+template <typename T> __device__ __forceinline__ double ld(const T* p, long long k) { return (double)p[k]; }
+
+// interior in the GLOBAL grid and with all four neighbours present locally
+__device__ __forceinline__ bool is_interior(const Geom& g, int i, int j) {
+    const int jg = g.jg0 + j;
+    return i >= 1 && i < g.ny - 1 && j >= 1 && j < g.nx - 1 && jg >= 1 && jg < g.nxg - 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// shared per-cell math
+// ------------------------------------------------------------------------------------------------
+// v5.py:149-162
+template <typename T>
+__device__ __forceinline__ double tau_cell(const Geom& g, double uc, double vc, double dt, double nu_eff) {
+    const double vel = sqrt(uc * uc + vc * vc);
+    double t;
+    if (vel > 1e-10) {
+        const double Pe = vel * g.hmin / (nu_eff + 1e-10);
+        t = g.hmin / (2 * vel) * fmin(1.0, Pe / 2.0);
+    } else {
+        t = dt / 2;
+    }
+    return Rnd<T>::r(t);
+}
+// v5.py:127-147
+template <typename T>
+__device__ __forceinline__ double conv_supg_cell(const Geom& g, double uc, double vc, double pc, double pe, double pw,
+                                                 double pn, double ps, double tau) {
+    double c = uc * ((pe - pw) * g.qdx) + vc * ((pn - ps) * g.qdy);
+    if (tau > 0) c -= tau * (uc * ((pe - 2 * pc + pw) * g.hdx2) + vc * ((pn - 2 * pc + ps) * g.hdy2));
+    return Rnd<T>::r(c);
+}
+// v5.py:112-125
+template <typename T>
+__device__ __forceinline__ double conv_upwind_cell(const Geom& g, double uc, double vc, double pc, double pe, double pw,
+                                                   double pn, double ps) {
+    const double dpx = uc > 0 ? (pc - pw) * g.rdx : (pe - pc) * g.rdx;
+    const double dpy = vc > 0 ? (pc - ps) * g.rdy : (pn - pc) * g.rdy;
+    return Rnd<T>::r(uc * dpx + vc * dpy);
+}
+// v5.py:164-176
+template <typename T>
+__device__ __forceinline__ double lap_cell(const Geom& g, double nu_eff, double pc, double pe, double pw, double pn, double ps) {
+    return Rnd<T>::r(nu_eff * ((pe - 2 * pc + pw) * g.ax + (pn - 2 * pc + ps) * g.ay));
+}
+
+// ------------------------------------------------------------------------------------------------
+// unit kernels
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void k_supg_tau(Geom g, const T* __restrict__ u, const T* __restrict__ v, T* __restrict__ tau, double dt,
+                           double nu_eff, const T* __restrict__ nu_t) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double out = 0.0;
+    if (is_interior(g, i, j)) {
+        const double ne = nu_t ? Rnd<T>::r(nu_eff + ld(nu_t, k)) : nu_eff;
+        out = tau_cell<T>(g, ld(u, k), ld(v, k), dt, ne);
+    }
+    tau[k] = (T)out;
+}
+
+template <typename T>
+__global__ void k_convection(Geom g, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ phi,
+                             const T* __restrict__ tau, T* __restrict__ conv, int supg) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double out = 0.0;
+    if (is_interior(g, i, j)) {
+        const double pc = ld(phi, k), pe = ld(phi, k + 1), pw = ld(phi, k - 1), pn = ld(phi, k + g.pitch), ps = ld(phi, k - g.pitch);
+        out = supg ? conv_supg_cell<T>(g, ld(u, k), ld(v, k), pc, pe, pw, pn, ps, ld(tau, k))
+                   : conv_upwind_cell<T>(g, ld(u, k), ld(v, k), pc, pe, pw, pn, ps);
+    }
+    conv[k] = (T)out;
+}
+
+template <typename T>
+__global__ void k_laplacian(Geom g, const T* __restrict__ phi, T* __restrict__ lap, double nu_eff, const T* __restrict__ nu_t) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double out = 0.0;
+    if (is_interior(g, i, j)) {
+        const double ne = nu_t ? Rnd<T>::r(nu_eff + ld(nu_t, k)) : nu_eff;
+        out = lap_cell<T>(g, ne, ld(phi, k), ld(phi, k + 1), ld(phi, k - 1), ld(phi, k + g.pitch), ld(phi, k - g.pitch));
+    }
+    lap[k] = (T)out;
+}
+
+// v5.py:178-187 (+ fused max|div| for the per-step log line v5.py:410)
+template <typename T>
+__global__ void k_divergence(Geom g, const T* __restrict__ u, const T* __restrict__ v, T* __restrict__ div,
+                             unsigned long long* max_out) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    double out = 0.0;
+    if (i < g.ny && j < g.nx) {
+        const long long k = i * g.pitch + j;
+        if (is_interior(g, i, j))
+            out = Rnd<T>::r((ld(u, k + 1) - ld(u, k - 1)) * g.hdx + (ld(v, k + g.pitch) - ld(v, k - g.pitch)) * g.hdy);
+        div[k] = (T)out;
+    }
+    if (max_out) block_atomic_max(fabs(out), max_out);
+}
+
+// v5.py:189-200
+template <typename T>
+__global__ void k_gradient(Geom g, const T* __restrict__ phi, T* __restrict__ gx, T* __restrict__ gy) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double ox = 0.0, oy = 0.0;
+    if (is_interior(g, i, j)) {
+        ox = (ld(phi, k + 1) - ld(phi, k - 1)) * g.hdx;
+        oy = (ld(phi, k + g.pitch) - ld(phi, k - g.pitch)) * g.hdy;
+    }
+    gx[k] = (T)ox;
+    gy[k] = (T)oy;
+}
+
+// v5.py:96-110 (forward differences)
+template <typename T>
+__global__ void k_smagorinsky(Geom g, const T* __restrict__ u, const T* __restrict__ v, T* __restrict__ nu_t, double csd2) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double out = 0.0;
+    if (is_interior(g, i, j)) {
+        const double uc = ld(u, k), vc = ld(v, k);
+        const double dudx = (ld(u, k + 1) - uc) / g.dx, dudy = (ld(u, k + g.pitch) - uc) / g.dy;
+        const double dvdx = (ld(v, k + 1) - vc) / g.dx, dvdy = (ld(v, k + g.pitch) - vc) / g.dy;
+        out = csd2 * sqrt(2 * (dudx * dudx + dvdy * dvdy) + (dudy + dvdx) * (dudy + dvdx));
+    }
+    nu_t[k] = (T)out;
+}
+
+// inflow profile value, v5.py:351-353
+__device__ __forceinline__ double inflow_u(double V_inf, double y_max, double yi, double pert_scale, double phase) {
+    return V_inf * (1 + pert_scale * sin(2 * M_PI * yi / y_max + phase));
+}
+
+// v5.py:349-360: one thread per border cell; order inflow, outflow, walls (corners end as 0)
+template <typename T>
+__global__ void k_apply_bc(Geom g, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ y, double V_inf,
+                           double y_max, double pert_scale, double phase) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < g.ny) {
+        const int i = t;
+        const bool wall = (i == 0 || i == g.ny - 1);
+        if (g.jg0 == 0) {
+            u[i * g.pitch] = wall ? (T)0 : (T)inflow_u(V_inf, y_max, y[i], pert_scale, phase);
+            v[i * g.pitch] = (T)0;
+        }
+        if (g.jg0 + g.nx == g.nxg) {
+            u[i * g.pitch + g.nx - 1] = wall ? (T)0 : u[i * g.pitch + g.nx - 2];
+            v[i * g.pitch + g.nx - 1] = wall ? (T)0 : v[i * g.pitch + g.nx - 2];
+        }
+    } else if (t < g.ny + g.nx) {
+        const int j = t - g.ny;
+        u[j] = (T)0; v[j] = (T)0;
+        u[(long long)(g.ny - 1) * g.pitch + j] = (T)0;
+        v[(long long)(g.ny - 1) * g.pitch + j] = (T)0;
+    }
+}
+
+// v5.py:228-237
+template <typename T>
+__global__ void k_apply_ibm(Geom g, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm, double fs) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    const double m = ibm[k];
+    if (m > 0) {
+        u[k] = (T)(ld(u, k) * (1.0 - m * fs));
+        v[k] = (T)(ld(v, k) * (1.0 - m * fs));
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// K1: fused momentum predictor  u*, v* = IBM(BC(u + dt(-C + L)))            v5.py:388-407
+// One thread per cell.  The thread of the global outflow column evaluates the predictor at column
+// nx-2 (BC copies the already predicted neighbour, v5.py:355-356); wall rows are 0; the global inflow
+// column takes the perturbed profile.  Local edge columns of a slab that are not global edges are halo
+// columns: they are not written here (the halo exchange fills them).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void predict_cell(const Geom& g, const Phys& p, const T* __restrict__ u,
+                                             const T* __restrict__ v, const T* __restrict__ nu_t, long long k,
+                                             double dt, double& ru, double& rv, double& tau_o) {
+    const double uc = ld(u, k), vc = ld(v, k);
+    const double ue = ld(u, k + 1), uw = ld(u, k - 1), un = ld(u, k + g.pitch), us = ld(u, k - g.pitch);
+    const double ve = ld(v, k + 1), vw = ld(v, k - 1), vn = ld(v, k + g.pitch), vs = ld(v, k - g.pitch);
+    const double ne = nu_t ? Rnd<T>::r(p.nu_eff + ld(nu_t, k)) : p.nu_eff;
+    double cu, cv;
+    if (p.use_supg) {
+        const double tau = tau_cell<T>(g, uc, vc, dt, ne);
+        tau_o = tau;
+        cu = conv_supg_cell<T>(g, uc, vc, uc, ue, uw, un, us, tau);
+        cv = conv_supg_cell<T>(g, uc, vc, vc, ve, vw, vn, vs, tau);
+    } else {
+        tau_o = 0.0;
+        cu = conv_upwind_cell<T>(g, uc, vc, uc, ue, uw, un, us);
+        cv = conv_upwind_cell<T>(g, uc, vc, vc, ve, vw, vn, vs);
+    }
+    const double lu = lap_cell<T>(g, ne, uc, ue, uw, un, us);
+    const double lv = lap_cell<T>(g, ne, vc, ve, vw, vn, vs);
+    ru = axpy_pred<T>(uc, dt, cu, lu);
+    rv = axpy_pred<T>(vc, dt, cv, lv);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BX* BY)
+k_predictor(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
+            T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const T* __restrict__ nu_t,
+            const double* __restrict__ ibm, const double* __restrict__ y) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const int jg = g.jg0 + j;
+    const long long k = i * g.pitch + j;
+    const bool wall = (i == 0 || i == g.ny - 1);
+    const bool inflow = (jg == 0), outflow = (jg == g.nxg - 1);
+    if (!inflow && !outflow && (j == 0 || j == g.nx - 1)) return;   // slab halo column
+    const double dt = ctl->dt, fs = ctl->fs;
+    double ru, rv, tau_o = 0.0;
+    if (wall) {
+        ru = 0.0; rv = 0.0;
+    } else if (inflow) {
+        ru = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase));
+        rv = 0.0;
+    } else if (outflow) {
+        double t;
+        if (jg - 1 == 0) { ru = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); rv = 0.0; }
+        else predict_cell<T>(g, p, u, v, nu_t, k - 1, dt, ru, rv, t);
+    } else {
+        predict_cell<T>(g, p, u, v, nu_t, k, dt, ru, rv, tau_o);
+    }
+    const double m = ibm[k];
+    if (m > 0) {
+        ru = Rnd<T>::r(ru * (1.0 - m * fs));
+        rv = Rnd<T>::r(rv * (1.0 - m * fs));
+    }
+    us[k] = (T)ru;
+    vs[k] = (T)rv;
+    if (tau_out) tau_out[k] = (T)tau_o;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: u = u* - dt grad(phi), fused max|grad phi|                              v5.py:413-417
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(BX* BY)
+k_correct(Geom g, StepCtl* __restrict__ ctl, const T* __restrict__ us, const T* __restrict__ vs,
+          const T* __restrict__ phi, T* __restrict__ u, T* __restrict__ v) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    double gm = 0.0;
+    if (i < g.ny && j < g.nx) {
+        const long long k = i * g.pitch + j;
+        const double dt = ctl->dt;
+        double gx = 0.0, gy = 0.0;
+        if (is_interior(g, i, j)) {
+            gx = Rnd<T>::r((ld(phi, k + 1) - ld(phi, k - 1)) * g.hdx);
+            gy = Rnd<T>::r((ld(phi, k + g.pitch) - ld(phi, k - g.pitch)) * g.hdy);
+        }
+        u[k] = (T)axmy<T>(ld(us, k), dt, gx);
+        v[k] = (T)axmy<T>(ld(vs, k), dt, gy);
+        gm = sqrt(Rnd<T>::r(Rnd<T>::r(gx * gx) + Rnd<T>::r(gy * gy)));
+    }
+    block_atomic_max(gm, &ctl->max_grad);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: finalize.  Reads ua, va (after clean_divergence), writes u, v (different buffers):
+//   max|div(ua,va)| (v5.py:421-422) -> BC (v5.py:424) -> IBM (:425) -> nanmax|vorticity| (:427-428)
+//   -> nanmean energy (:431-432) -> clip (:437-438) -> post-clip max|u|,|v| for the next adaptive dt.
+// BC+IBM are pointwise in (ua, va), so the vorticity stencil re-evaluates them at the 4 neighbours.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void bcibm_cell(const Geom& g, const Phys& p, const StepCtl* ctl, const T* __restrict__ ua,
+                                           const T* __restrict__ va, const double* __restrict__ ibm,
+                                           const double* __restrict__ y, int i, int j, double& fu, double& fv) {
+    const int jg = g.jg0 + j;
+    const long long k = i * g.pitch + j;
+    if (i == 0 || i == g.ny - 1) { fu = 0.0; fv = 0.0; }
+    else if (jg == 0) { fu = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); fv = 0.0; }
+    else if (jg == g.nxg - 1) {
+        if (jg - 1 == 0) { fu = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); fv = 0.0; }
+        else { fu = ld(ua, k - 1); fv = ld(va, k - 1); }
+    } else { fu = ld(ua, k); fv = ld(va, k); }
+    const double m = ibm[k];
+    if (m > 0) {
+        fu = Rnd<T>::r(fu * (1.0 - m * ctl->fs));
+        fv = Rnd<T>::r(fv * (1.0 - m * ctl->fs));
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BX* BY)
+k_finalize(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
+           T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm, const uint8_t* __restrict__ mask,
+           const double* __restrict__ y, double* __restrict__ ke_part, unsigned long long* __restrict__ cnt_part) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    double dmax = 0.0, wmax = 0.0, e = 0.0, mu = 0.0, mv = 0.0;
+    unsigned cnt = 0, bad = 0;
+    const bool own = i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg));
+    if (own) {
+        const long long k = i * g.pitch + j;
+        double fu, fv;
+        bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j, fu, fv);
+        if (is_interior(g, i, j)) {
+            dmax = fabs(Rnd<T>::r((ld(ua, k + 1) - ld(ua, k - 1)) * g.hdx + (ld(va, k + g.pitch) - ld(va, k - g.pitch)) * g.hdy));
+            if (!(mask && mask[k])) {
+                double eu, ev, wu, wv, nu_, nv, su, sv;
+                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j + 1, eu, ev);
+                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j - 1, wu, wv);
+                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i + 1, j, nu_, nv);
+                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i - 1, j, su, sv);
+                const double w = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(ev - wv) / Rnd<T>::r(g.two_dx)) -
+                                           Rnd<T>::r(Rnd<T>::r(nu_ - su) / Rnd<T>::r(g.two_dy)));
+                wmax = fabs(w);   // NaN is dropped by fmax in the reduction (nanmax)
+            }
+        }
+        const double en = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fu * fu) + Rnd<T>::r(fv * fv)));
+        if (en == en) { e = en; cnt = 1; }
+        if (!isfinite(fu) || !isfinite(fv)) bad = 1;
+        const double cu = fmin(fmax(fu, -p.max_velocity), p.max_velocity);
+        const double cv = fmin(fmax(fv, -p.max_velocity), p.max_velocity);
+        // np.clip propagates NaN; fmin/fmax would drop it
+        u[k] = (T)(fu == fu ? cu : fu);
+        v[k] = (T)(fv == fv ? cv : fv);
+        mu = fabs(cu); mv = fabs(cv);
+    }
+    block_atomic_max(dmax, &ctl->max_div_post);
+    block_atomic_max(wmax, &ctl->max_vort);
+    block_atomic_max(mu, &ctl->max_u);
+    block_atomic_max(mv, &ctl->max_v);
+    const double bs = block_sum(e);
+    const double bc = block_sum((double)cnt);
+    const int nbad = __syncthreads_or((int)bad);
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        const int b = blockIdx.y * gridDim.x + blockIdx.x;
+        ke_part[b] = bs;
+        cnt_part[b] = (unsigned long long)(bc + 0.5);
+        if (nbad) atomicOr(&ctl->nonfinite, 1u);
+    }
+}
+
+// max|u|, max|v| of the bound state (set_step / first step: what adaptive_time_step reads, v5.py:322)
+template <typename T>
+__global__ void k_max_abs2(Geom g, const T* __restrict__ u, const T* __restrict__ v, StepCtl* ctl) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    double mu = 0.0, mv = 0.0;
+    if (i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg))) {
+        mu = fabs(ld(u, i * g.pitch + j)); mv = fabs(ld(v, i * g.pitch + j));
+    }
+    block_atomic_max(mu, &ctl->max_u);
+    block_atomic_max(mv, &ctl->max_v);
+}
+
+// monitor_simulation_health (v5.py:599-613): non-finite flag, max|u|, max|v|, max|div(u,v)| of the state
+// out[0..3] = {nonfinite, max|u|, max|v|, max|div|} as order-preserving bit patterns (zeroed by the launcher)
+template <typename T>
+__global__ void __launch_bounds__(BX* BY)
+k_health(Geom g, const T* __restrict__ u, const T* __restrict__ v, unsigned long long* __restrict__ out) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    double mu = 0.0, mv = 0.0, md = 0.0;
+    int bad = 0;
+    if (i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg))) {
+        const long long k = i * g.pitch + j;
+        const double a = ld(u, k), b = ld(v, k);
+        bad = !isfinite(a) || !isfinite(b);
+        mu = fabs(a); mv = fabs(b);
+        if (is_interior(g, i, j))
+            md = fabs(Rnd<T>::r((ld(u, k + 1) - ld(u, k - 1)) * g.hdx + (ld(v, k + g.pitch) - ld(v, k - g.pitch)) * g.hdy));
+    }
+    block_atomic_max(mu, out + 1);
+    block_atomic_max(mv, out + 2);
+    block_atomic_max(md, out + 3);
+    if (__syncthreads_or(bad) && threadIdx.x == 0 && threadIdx.y == 0) atomicMax(out, 0x3ff0000000000000ull);  // 1.0
+}
+
+// ------------------------------------------------------------------------------------------------
+// device-resident step control                                                v5.py:316-326,351-352,406
+// ------------------------------------------------------------------------------------------------
+__device__ void ctl_prepare(StepCtl* c, const CtlParams& cp) {
+    const long long step = c->step;
+    double dt;
+    if (!cp.adaptive_dt) dt = cp.dt_base;
+    else if (step < 1000) dt = (double)(float)0.00002;
+    else {
+        double vm = fmax(fmax(c->in_max_u, c->in_max_v), 1e-10);
+        const double dt_cfl = cp.cfl_target * cp.hmin / vm;
+        const double nu_total = cp.is_f32 ? (double)(float)((float)((float)cp.nu + (float)c->in_mean_nut) + (float)cp.av)
+                                          : (cp.nu + c->in_mean_nut) + cp.av;
+        const double dt_visc = 0.4 * (cp.hmin * cp.hmin) / nu_total;
+        dt = fmin(dt_cfl, dt_visc);
+        dt = fmin(fmax(dt, cp.dt_min), cp.dt_max);
+        dt = (double)(float)dt;
+    }
+    c->dt = dt;
+    c->fs = fmin(1.0, (double)step / (double)cp.initial_steps);
+    c->pert_scale = fmin(1.0, (double)step / 1000.0) * 0.01;
+    c->phase = 0.02 * (double)step;
+    c->max_div_pre = c->max_grad = c->max_div_post = c->max_vort = c->max_u = c->max_v = 0ull;
+    c->nonfinite = 0u;
+    c->pois_change = 0ull; c->pois_last = 0.0; c->pois_iters = 0; c->pois_done = 0; c->pois_blocks_done = 0u;
+}
+
+__global__ void k_ctl_init(StepCtl* c, CtlParams cp, long long step, int use_measured_max) {
+    if (threadIdx.x || blockIdx.x) return;
+    c->step = step;
+    if (use_measured_max) { c->in_max_u = bits_to_double(c->max_u); c->in_max_v = bits_to_double(c->max_v); }
+    c->in_mean_nut = 0.0;
+    ctl_prepare(c, cp);
+}
+
+__global__ void k_ctl_zero_max(StepCtl* c) { if (!threadIdx.x && !blockIdx.x) { c->max_u = 0ull; c->max_v = 0ull; } }
+
+// closes a step: fixed-order sum of the energy partials, ring record, next step's dt / ramps
+__global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
+                               const unsigned long long* __restrict__ cnt_part, int n_part, StepScalars* ring, int cap) {
+    __shared__ double s_e[256];
+    __shared__ unsigned long long s_c[256];
+    double e = 0.0; unsigned long long n = 0;
+    for (int b = threadIdx.x; b < n_part; b += 256) { e += ke_part[b]; n += cnt_part[b]; }
+    s_e[threadIdx.x] = e; s_c[threadIdx.x] = n;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { s_e[threadIdx.x] += s_e[threadIdx.x + o]; s_c[threadIdx.x] += s_c[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x) return;
+    StepScalars r;
+    r.dt = c->dt;
+    r.max_div_pre = bits_to_double(c->max_div_pre);
+    r.max_grad_phi = bits_to_double(c->max_grad);
+    r.max_div_post = bits_to_double(c->max_div_post);
+    r.max_vorticity = bits_to_double(c->max_vort);
+    r.mean_energy = s_c[0] ? s_e[0] / (double)s_c[0] : __longlong_as_double(0x7ff8000000000000ll);
+    r.max_abs_u = bits_to_double(c->max_u);
+    r.max_abs_v = bits_to_double(c->max_v);
+    r.poisson_iters = (double)c->pois_iters;
+    r.poisson_change = c->pois_last;
+    r.nonfinite = (double)c->nonfinite;
+    r.step = (double)c->step;
+    ring[(int)(c->step % cap)] = r;
+    c->in_max_u = r.max_abs_u; c->in_max_v = r.max_abs_v;
+    c->step += 1;
+    ctl_prepare(c, cp);
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+#define DISPATCH(dtype, CALL_F64, CALL_F32) do { if ((dtype) == 0) { CALL_F64; } else { CALL_F32; } } while (0)
+
+void launch_supg_tau(int dtype, const Geom& g, const void* u, const void* v, void* tau, double dt, double nu_eff,
+                     const void* nu_t, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_supg_tau<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, (double*)tau, dt, nu_eff, (const double*)nu_t)),
+             (k_supg_tau<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, (float*)tau, dt, nu_eff, (const float*)nu_t)));
+}
+void launch_convection(int dtype, const Geom& g, const void* u, const void* v, const void* phi, const void* tau,
+                       void* conv, int supg, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_convection<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, (const double*)phi, (const double*)tau, (double*)conv, supg)),
+             (k_convection<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, (const float*)phi, (const float*)tau, (float*)conv, supg)));
+}
+void launch_laplacian(int dtype, const Geom& g, const void* phi, void* lap, double nu_eff, const void* nu_t, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_laplacian<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)phi, (double*)lap, nu_eff, (const double*)nu_t)),
+             (k_laplacian<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)phi, (float*)lap, nu_eff, (const float*)nu_t)));
+}
+void launch_divergence(int dtype, const Geom& g, const void* u, const void* v, void* div, unsigned long long* max_out,
+                       cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_divergence<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, (double*)div, max_out)),
+             (k_divergence<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, (float*)div, max_out)));
+}
+void launch_gradient(int dtype, const Geom& g, const void* phi, void* gx, void* gy, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_gradient<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)phi, (double*)gx, (double*)gy)),
+             (k_gradient<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)phi, (float*)gx, (float*)gy)));
+}
+void launch_smagorinsky(int dtype, const Geom& g, const void* u, const void* v, void* nu_t, double cs, cudaStream_t s) {
+    const double delta = sqrt(g.dx * g.dy);
+    const double csd2 = (cs * delta) * (cs * delta);
+    DISPATCH(dtype,
+             (k_smagorinsky<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, (double*)nu_t, csd2)),
+             (k_smagorinsky<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, (float*)nu_t, csd2)));
+}
+void launch_apply_bc(int dtype, const Geom& g, void* u, void* v, const double* y, double V_inf, double y_max,
+                     long long step, cudaStream_t s) {
+    const double sc = (double)step / 1000.0;
+    const double pert_scale = (sc < 1.0 ? sc : 1.0) * 0.01, phase = 0.02 * (double)step;
+    const int n = g.ny + g.nx;
+    DISPATCH(dtype,
+             (k_apply_bc<double><<<(n + 255) / 256, 256, 0, s>>>(g, (double*)u, (double*)v, y, V_inf, y_max, pert_scale, phase)),
+             (k_apply_bc<float><<<(n + 255) / 256, 256, 0, s>>>(g, (float*)u, (float*)v, y, V_inf, y_max, pert_scale, phase)));
+}
+void launch_apply_ibm(int dtype, const Geom& g, void* u, void* v, const double* ibm, double fs, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_apply_ibm<double><<<grid2d(g), kBlock, 0, s>>>(g, (double*)u, (double*)v, ibm, fs)),
+             (k_apply_ibm<float><<<grid2d(g), kBlock, 0, s>>>(g, (float*)u, (float*)v, ibm, fs)));
+}
+void launch_predictor(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
+                      void* us, void* vs, void* tau, const void* nu_t, const double* ibm, const double* y, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_predictor<double><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const double*)u, (const double*)v, (double*)us, (double*)vs, (double*)tau, (const double*)nu_t, ibm, y)),
+             (k_predictor<float><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const float*)u, (const float*)v, (float*)us, (float*)vs, (float*)tau, (const float*)nu_t, ibm, y)));
+}
+void launch_correct(int dtype, const Geom& g, StepCtl* ctl, const void* us, const void* vs, const void* phi,
+                    void* u, void* v, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_correct<double><<<grid2d(g), kBlock, 0, s>>>(g, ctl, (const double*)us, (const double*)vs, (const double*)phi, (double*)u, (double*)v)),
+             (k_correct<float><<<grid2d(g), kBlock, 0, s>>>(g, ctl, (const float*)us, (const float*)vs, (const float*)phi, (float*)u, (float*)v)));
+}
+int finalize_num_partials(const Geom& g) { dim3 gr = grid2d(g); return (int)(gr.x * gr.y); }
+void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
+                     void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
+                     double* ke_partials, unsigned long long* cnt_partials, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_finalize<double><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const double*)ua, (const double*)va, (double*)u, (double*)v, ibm, mask, y, ke_partials, cnt_partials)),
+             (k_finalize<float><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const float*)ua, (const float*)va, (float*)u, (float*)v, ibm, mask, y, ke_partials, cnt_partials)));
+}
+void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s) {
+    k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max);
+}
+void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* ke_partials,
+                         const unsigned long long* cnt_partials, int n_partials, StepScalars* ring, int ring_cap,
+                         cudaStream_t s) {
+    k_ctl_end_step<<<1, 256, 0, s>>>(ctl, cp, ke_partials, cnt_partials, n_partials, ring, ring_cap);
+}
+void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s) {
+    cudaMemsetAsync(out4, 0, 4 * sizeof(unsigned long long), s);
+    DISPATCH(dtype,
+             (k_health<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, out4)),
+             (k_health<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, out4)));
+}
+void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, StepCtl* ctl, cudaStream_t s) {
+    k_ctl_zero_max<<<1, 32, 0, s>>>(ctl);
+    DISPATCH(dtype,
+             (k_max_abs2<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, ctl)),
+             (k_max_abs2<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, ctl)));
+}
+
+}  // namespace b200cfd

@@ -1,0 +1,241 @@
+"""GPU parity: the CUDA path (through the C ABI) against (i) goldens minted from the reference itself
+(tests/golden, NUMBA_NUM_THREADS=1) and (ii) the C oracle on seeded inputs.
+Tolerances (north_star): rel-L2 <= 1e-12 in fp64, <= 1e-5 in fp32 (u, v); phi gets 10x in fp32 (SURVEY finding 8)."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"f64": 1e-12, "f32": 1e-5}
+
+
+def load(name):
+    d = np.load(GOLDEN / name)
+    return d, json.loads(str(d["meta"]))
+
+
+@pytest.fixture(scope="module")
+def K():
+    from cfd_simulations_b200 import kernels
+    return kernels
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import orc as o
+    return o
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+@pytest.mark.parametrize("shape", ["12x16", "37x53"])
+def test_kernels_vs_reference_golden(K, tag, shape):
+    g, _ = load(f"kernels_{shape}_{tag}.npz")
+    tol = TOL[tag]
+    u, v, phi = g["u"], g["v"], g["phi"]
+    dx, dy, dt, nu_eff = float(g["dx"]), float(g["dy"]), float(g["dt"]), float(g["nu_eff"])
+    assert rel_l2(K.compute_supg_stabilization_fast(u, v, dx, dy, dt, nu_eff), g["tau"]) <= tol
+    assert rel_l2(K.compute_convection_supg_fast(u, v, phi, dx, dy, g["tau"]), g["conv_supg"]) <= tol
+    assert rel_l2(K.compute_convection_fast(u, v, phi, dx, dy), g["conv_upwind"]) <= tol
+    assert rel_l2(K.compute_laplacian_fast(phi, dx, dy, nu_eff), g["lap"]) <= tol
+    assert rel_l2(K.compute_divergence_fast(u, v, dx, dy), g["div"]) <= tol
+    gx, gy = K.compute_gradient_fast(phi, dx, dy)
+    assert rel_l2(gx, g["gx"]) <= tol and rel_l2(gy, g["gy"]) <= tol
+    assert rel_l2(K.compute_smagorinsky_viscosity_fast(u, v, dx, dy, 0.17), g["smag"]) <= tol
+    ui, vi = u.copy(), v.copy()
+    K.apply_ibm_fast(ui, vi, g["ibm"], 0.37)
+    assert rel_l2(ui, g["ibm_u"]) <= tol and rel_l2(vi, g["ibm_v"]) <= tol
+    ub, vb = u.copy(), v.copy()
+    K.apply_boundary_conditions(ub, vb, g["y"], 4.0, 1.0, int(g["bc_step"]))
+    assert rel_l2(ub, g["bc_u"]) <= tol and rel_l2(vb, g["bc_v"]) <= tol
+    cdt = float(np.float32(5e-5))
+    p = K.solve_pressure_gauss_seidel_fast(np.zeros_like(u), g["div"], dx, dy, cdt, g["mask"], 1, 1e-8, mode="as_executed")
+    assert rel_l2(p, g["rbgs_as_executed"]) <= tol
+    p, it, _ = K.solve_pressure_gauss_seidel_fast(np.zeros_like(u), g["div"], dx, dy, cdt, g["mask"], 40, 0.0,
+                                                  return_info=True, temporal_depth=1)
+    assert it == 40 and rel_l2(p, g["rbgs_fixed40"]) <= tol
+    p, it, last = K.solve_pressure_gauss_seidel_fast(np.zeros_like(u), g["div"], dx, dy, cdt, g["mask"], 100000,
+                                                     float(g["rbgs_tol_value"]), return_info=True)
+    assert it == int(g["rbgs_tol_iters"]), (it, int(g["rbgs_tol_iters"]))
+    assert rel_l2(p, g["rbgs_tol"]) <= tol
+    uc, vc = u.copy(), v.copy()
+    K.clean_divergence_fast(uc, vc, dx, dy, 2)
+    assert rel_l2(uc, g["clean_u"]) <= tol and rel_l2(vc, g["clean_v"]) <= tol
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_jacobi_branch_vs_reference_golden(K, tag):
+    g, _ = load(f"jacobi_24x64_{tag}.npz")
+    for depth in (1, 0):
+        phi = K.solve_pressure_jacobi(np.zeros_like(g["div"]), g["div"], float(g["dx"]), float(g["dt"]), g["mask"],
+                                      int(g["sweeps"]), temporal_depth=depth)
+        assert rel_l2(phi, g["phi"]) <= TOL[tag], depth
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+@pytest.mark.parametrize("shape,dxdy", [((300, 700), (0.03, 0.02)), ((257, 1031), (0.01, 0.01)), ((96, 200), (0.004, 0.03)),
+                                        ((64, 4100), (0.02, 0.005))])
+def test_clean_divergence_lexicographic_vs_oracle(K, orc, tag, shape, dxdy):
+    """The overlapped-tile sweep must reproduce the sequential lexicographic Gauss-Seidel sweep."""
+    rng = np.random.default_rng(5)
+    dt = np.float64 if tag == "f64" else np.float32
+    u = rng.standard_normal(shape).astype(dt)
+    v = rng.standard_normal(shape).astype(dt)
+    dx, dy = dxdy
+    ur, vr, pr = orc.clean_divergence_fast(u.copy(), v.copy(), dx, dy, 2, return_psi=True)
+    ug, vg, pg = K.clean_divergence_fast(u.copy(), v.copy(), dx, dy, 2, return_psi=True)
+    tol = TOL[tag]
+    assert rel_l2(pg, pr) <= tol * (1 if tag == "f64" else 3)
+    assert rel_l2(ug, ur) <= tol and rel_l2(vg, vr) <= tol
+
+
+def test_clean_divergence_redblack_reduces_divergence(K, orc):
+    rng = np.random.default_rng(6)
+    u = rng.standard_normal((128, 256)); v = rng.standard_normal((128, 256))
+    d0 = np.abs(orc.compute_divergence_fast(u, v, 0.02, 0.02)).max()
+    ug, vg = K.clean_divergence_fast(u.copy(), v.copy(), 0.02, 0.02, 2, mode="redblack")
+    assert np.isfinite(ug).all() and np.abs(ug - u).max() > 0
+    assert np.abs(orc.compute_divergence_fast(ug, vg, 0.02, 0.02))[2:-2, 2:-2].max() < 2 * d0
+
+
+@pytest.mark.parametrize("tag", ["f64", "f32"])
+def test_poisson_modes_vs_oracle(K, orc, tag):
+    rng = np.random.default_rng(3)
+    dt = np.float64 if tag == "f64" else np.float32
+    ny, nx = 130, 258
+    div = (0.1 * rng.standard_normal((ny, nx))).astype(dt)
+    yy, xx = np.mgrid[0:ny, 0:nx]
+    mask = (xx - nx / 5) ** 2 + (yy - ny / 2) ** 2 <= (ny / 8) ** 2
+    dx, dy, cdt = 1.0 / (nx - 1), 1.3 / (ny - 1), float(np.float32(5e-5))
+    tol = TOL[tag]
+    for omega, iters in ((1.0, 37), (1.5, 24)):
+        pr, _, lr = orc.solve_pressure_gauss_seidel(np.zeros((ny, nx), dt), div, dx, dy, cdt, mask, iters, 0.0, omega)
+        for depth in (1, 0):
+            pg, it, lg = K.solve_pressure_gauss_seidel_fast(np.zeros((ny, nx), dt), div, dx, dy, cdt, mask, iters, 0.0,
+                                                            omega=omega, return_info=True, temporal_depth=depth)
+            assert rel_l2(pg, pr) <= tol * (1 if tag == "f64" else 20), (omega, depth)
+    # tolerance-terminated: same iteration count as the oracle
+    tolv = 2e-2 * float(np.abs(div).max()) / cdt * dx * dx
+    pr, itr, lr = orc.solve_pressure_gauss_seidel(np.zeros((ny, nx), dt), div, dx, dy, cdt, mask, 5000, tolv, 1.0)
+    pg, itg, lg = K.solve_pressure_gauss_seidel_fast(np.zeros((ny, nx), dt), div, dx, dy, cdt, mask, 5000, tolv,
+                                                     return_info=True)
+    assert 1 < itr < 5000
+    if tag == "f64":
+        assert itg == itr and abs(lg - lr) <= 1e-9 * abs(lr)
+    else:
+        assert abs(itg - itr) <= max(2, itr // 50)
+    assert rel_l2(pg, pr) <= tol * (1 if tag == "f64" else 50)
+    # Jacobi branch (dx only), plain and temporally blocked
+    pr = orc.solve_pressure_jacobi(np.zeros((ny, nx), dt), div, dx, cdt, mask, 61)
+    for depth in (1, 0, 3):
+        pg = K.solve_pressure_jacobi(np.zeros((ny, nx), dt), div, dx, cdt, mask, 61, temporal_depth=depth)
+        assert rel_l2(pg, pr) <= tol * (1 if tag == "f64" else 5), depth
+
+
+def _gpu_steps(name, nx, ny, f32, nsteps, snaps, **kw):
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    g, _ = load(name)
+    cfg = OptimizedTurbulentConfig(nx=nx, ny=ny, memory_efficient=f32, **kw)
+    s = OptimizedTurbulentSolver(cfg)
+    assert rel_l2(s.u, g["u0"]) < 1e-15
+    s.step = int(g["start_step"])
+    tol = TOL["f32" if f32 else "f64"]
+    for k in range(1, nsteps + 1):
+        dt = s.time_step()
+        assert float(dt) == float(g["dts"][k - 1]), k
+        if k in snaps:
+            assert rel_l2(s.u, g[f"u_{k}"]) <= tol, k
+            assert rel_l2(s.v, g[f"v_{k}"]) <= tol * (1 if not f32 else 3), k
+            assert rel_l2(s.phi, g[f"phi_{k}"]) <= tol * (1 if not f32 else 10), k
+    e = np.array([x for _, x in s.energy_history])
+    assert np.allclose(e, g["energy"], rtol=1e-12 if not f32 else 1e-5)
+    s.close()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_from0_vs_reference_golden(f32):
+    _gpu_steps(f"steps_46x150_from0_{'f32' if f32 else 'f64'}.npz", 150, 46, f32, 100, {1, 10, 100})
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_across_step1000_switch_vs_reference_golden(f32):
+    _gpu_steps(f"steps_46x150_from990_{'f32' if f32 else 'f64'}.npz", 150, 46, f32, 25, {25})
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_shipped_grid_vs_reference_golden(f32):
+    _gpu_steps(f"steps_180x600_from0_{'f32' if f32 else 'f64'}.npz", 600, 180, f32, 10, {10})
+
+
+def test_steps_upwind_branch_vs_reference_golden():
+    _gpu_steps("steps_30x90_upwind_f64.npz", 90, 30, False, 10, {10}, use_supg=False)
+
+
+@pytest.mark.parametrize("f32,graph", [(False, True), (False, False), (True, True)])
+def test_steps_vs_oracle_medium_grid(f32, graph):
+    """1024x256, 30 steps (+ 15 more across the step-1000 switch), CUDA graph replay vs per-kernel launches;
+    all five logged scalars are compared as well."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=1024, ny=256, memory_efficient=f32)
+    so, sg = OracleTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg, use_graph=graph)
+    tol = TOL["f32" if f32 else "f64"]
+    for start, n in ((0, 30), (990, 15)):
+        if start:
+            so.step = start
+            sg.u, sg.v = so.u, so.v
+            sg.step = start
+        for _ in range(n):
+            so.time_step()
+        sg.advance(n)
+        assert rel_l2(sg.u, so.u) <= tol and rel_l2(sg.v, so.v) <= tol * (1 if not f32 else 3)
+        assert rel_l2(sg.phi, so.phi) <= tol * (1 if not f32 else 10)
+        assert rel_l2(sg.u_star, so.u_star) <= tol and rel_l2(sg.div_u_star, so.div_u_star) <= tol * (1 if not f32 else 100)
+        assert rel_l2(sg.tau_supg, so.tau_supg) <= tol
+        sg._sync_scalars()
+        rt = 1e-9 if not f32 else 2e-4
+        for k in range(1, n + 1):
+            a, b = sg.scalars[-k], so.scalars[-k]
+            assert a["dt"] == b[0]
+            for key, idx in (("max_div_pre", 1), ("max_grad_phi", 2), ("max_div_post", 3), ("max_vorticity", 4),
+                             ("mean_energy", 5), ("poisson_change", 7)):
+                assert abs(a[key] - b[idx]) <= rt * max(abs(b[idx]), 1e-30), (key, k, a[key], b[idx])
+            assert a["poisson_iters"] == b[6]
+    from cfd_simulations_b200.solver import monitor_simulation_health
+    assert monitor_simulation_health(sg, sg.step)
+    sg.close()
+
+
+@pytest.mark.parametrize("mode", ["as_written", "jacobi"])
+def test_steps_other_poisson_modes_vs_oracle(mode):
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=200, ny=64, memory_efficient=False, pressure_iterations=25,
+                                   use_fast_pressure=(mode != "jacobi"), pressure_tolerance=1e-8)
+    so = OracleTurbulentSolver(cfg, poisson_mode=mode)
+    sg = OptimizedTurbulentSolver(cfg, poisson_mode=mode)
+    for _ in range(5):
+        so.time_step()
+    sg.advance(5)
+    assert rel_l2(sg.u, so.u) <= 1e-12 and rel_l2(sg.v, so.v) <= 1e-12 and rel_l2(sg.phi, so.phi) <= 1e-12
+    sg.close()
+
+
+def test_time_step_host_round_trip_matches_resident():
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=300, ny=100, memory_efficient=False)
+    a, b = OptimizedTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg)
+    a.advance(6)
+    uh, vh = b.u, b.v
+    for _ in range(3):
+        last = b.time_step_host(uh, vh, 2)
+    assert np.array_equal(uh, a.u) and np.array_equal(vh, a.v)
+    assert last.step == 5
+    a.close(); b.close()

@@ -157,6 +157,110 @@ def run_reference_arm(args):
     print(json.dumps(line), flush=True)
 
 
+def slab_config(nx_global, ny, h=1.0 / 1024):
+    """BASELINE.json configs[3]: the cylinder/channel case weak-scaled along x, ny x (nx per GPU * N) cells with the
+    spacing fixed at h (the reference's warm-up dt = 2e-5 needs h >= 4.6e-4), cylinder at x = 4 in the
+    first slab, mid-height."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    y_max = (ny - 1) * h
+    return OptimizedTurbulentConfig(nx=nx_global, ny=ny, memory_efficient=False, x_min=0.0, x_max=(nx_global - 1) * h,
+                                    y_min=0.0, y_max=y_max, cylinder_center=(4.0, y_max / 2))
+
+
+def time_slab_steps(s, steps, warmup, world):
+    """warmup + timed steps of a (possibly decomposed) solver: barrier + synchronize on both sides, CUDA events,
+    max over ranks.  Returns milliseconds for `steps` steps."""
+    import torch
+    import torch.distributed as dist
+    s.advance(warmup)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    s.advance(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=s.device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+def run_slabs(args):
+    """N > 1: one process per GPU (torchrun), x-slabs of slab_nx x slab_ny cells per GPU (weak scaling)."""
+    import torch
+    import torch.distributed as dist
+    if "RANK" not in os.environ:
+        # launched as plain `python bench.py --gpus N`: re-launch under torchrun on this node
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29533", __file__] + sys.argv[1:]
+        return subprocess.call(cmd)
+    world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    nxs, ny = args.slab_nx, args.slab_ny
+    cfg = slab_config(nxs * world, ny)
+    s = OptimizedTurbulentSolver(cfg, device=local, nranks=world, rank=rank, setup="device")
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = time_slab_steps(s, args.steps, args.warmup, world)
+    clocks = sampler.stop() if rank == 0 else None
+    cells = nxs * world * ny
+    value = cells * args.steps / (ms * 1e-3) / 1e6
+    # end to end: every step uploads this slab's u, v from pinned host memory, steps, downloads them and the scalars
+    n_e2e = max(1, min(args.steps, 3))
+    uh = torch.empty_like(s.device_tensor("u"), device="cpu").pin_memory()
+    vh = torch.empty_like(uh).pin_memory()
+    uh.copy_(s.device_tensor("u")); vh.copy_(s.device_tensor("v"))
+    torch.cuda.synchronize(); dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(n_e2e):
+        s.device_tensor("u").copy_(uh, non_blocking=True); s.device_tensor("v").copy_(vh, non_blocking=True)
+        s.advance(1)
+        uh.copy_(s.device_tensor("u"), non_blocking=True); vh.copy_(s.device_tensor("v"), non_blocking=True)
+        s._sync_scalars()
+        torch.cuda.synchronize()
+    dist.barrier()
+    t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=s.device)
+    dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
+    t_e2e = float(t_e2e.item())
+    slab_bytes = uh.numel() * 8 * 2
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        step_bytes = sum(ALGO_BYTES.values()) * cells
+        ach = step_bytes / (ms / args.steps * 1e-3) / 1e9 / world
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"cylinder/channel case weak-scaled along x: {nxs}x{ny} cells per GPU slab, fp64, "
+                                       f"h = 1/1024 (BASELINE.json configs[3]); global grid {nxs * world}x{ny}",
+                           "poisson_mode": "as_executed", "cleandiv_mode": "lexicographic",
+                           "decomposition": {"halo_left": s.plan.halo_left if rank else s.plan.send_right,
+                                             "halo_right": s.plan.halo_right, "exchanges_per_step": 1,
+                                             "halo_bytes_per_step_per_gpu": s._halo.bytes_per_exchange,
+                                             "collectives_per_step": "1 all_gather (128 B/rank) + 1 batched send/recv"},
+                           "l2": f"working set {13 * nxs * ny * 8 / 1e9:.1f} GB per GPU >> 126 MB L2"},
+                "clocks": clocks,
+                "e2e": {"value": cells * n_e2e / t_e2e / 1e6, "unit": UNIT, "h2d_bytes_per_step": slab_bytes * world,
+                        "d2h_bytes_per_step": slab_bytes * world + 96 * world, "steps": n_e2e,
+                        "ms_per_step": t_e2e / n_e2e * 1e3,
+                        "note": "every step, every rank: pinned-host slab u,v -> HBM, time step, HBM -> host u,v + scalars"},
+                "gpu_launches": (s.launches_per_step() + 8) * args.steps * world,
+                "roofline": {"bound": "hbm", "kernel": "whole step (sum of phases)", "achieved": ach, "peak": peak,
+                             "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                             "note": "per GPU: algorithmic bytes of all phases / step time"},
+                "cpu_baseline": None}
+        print(json.dumps(line), flush=True)
+    s.close()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -167,6 +271,9 @@ def main():
     ap.add_argument("--ny", type=int, default=NY)
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for cpu_baseline")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--slab-nx", type=int, default=16384, help="columns per GPU slab (N > 1, weak scaling)")
+    ap.add_argument("--slab-ny", type=int, default=16384)
+    ap.add_argument("--no-scaling-base", action="store_true", help="skip the 1-GPU run of one weak-scaling slab")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -179,8 +286,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1 or args.gpus > 1:
-        from cfd_simulations_b200 import multigpu
-        return multigpu.bench_main(args, METRIC, UNIT)
+        return run_slabs(args)
 
     from cfd_simulations_b200.config import OptimizedTurbulentConfig
     from cfd_simulations_b200.solver import OptimizedTurbulentSolver
@@ -261,8 +367,21 @@ def main():
                        "l2": "working set 336 MB > 126 MB L2; no flush between steps (each step streams all fields)",
                        "clean_plan": s.clean_plan()},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(line), flush=True)
     s.close()
+    if not args.no_scaling_base:
+        # the 1-GPU point of the weak-scaling series (same slab as `--gpus N` uses per GPU), so that scaling efficiency
+        # can be formed against the SAME per-GPU workload: value(N) / (N * scaling_base.value)
+        del s
+        torch.cuda.empty_cache()
+        cfgs = slab_config(args.slab_nx, args.slab_ny)
+        sb = OptimizedTurbulentSolver(cfgs, device=local, setup="device")
+        nb = max(5, min(args.steps, 30))
+        msb = time_slab_steps(sb, nb, 3, 1)
+        line["scaling_base"] = {"workload": f"{args.slab_nx}x{args.slab_ny} fp64 slab on 1 GPU (BASELINE.json configs[3] per-GPU share)",
+                                "value": args.slab_nx * args.slab_ny * nb / (msb * 1e-3) / 1e6, "unit": UNIT,
+                                "ms_per_step": msb / nb, "steps": nb}
+        sb.close()
+    print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":

@@ -34,7 +34,7 @@ class Config(C.Structure):
         ("cs", C.c_double),
         ("pressure_tolerance", C.c_double), ("omega", C.c_double),
         ("rank", C.c_int32), ("nranks", C.c_int32), ("nx_global", C.c_int32), ("x_offset", C.c_int32),
-        ("halo", C.c_int32), ("reserved", C.c_int32),
+        ("halo_left", C.c_int32), ("halo_right", C.c_int32),
     ]
 
 
@@ -52,6 +52,8 @@ EXPORTS = [
     "b200cfd_k_supg_tau", "b200cfd_k_convection", "b200cfd_k_laplacian", "b200cfd_k_divergence",
     "b200cfd_k_gradient", "b200cfd_k_smagorinsky", "b200cfd_k_apply_bc", "b200cfd_k_apply_ibm",
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
+    "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len",
+    "b200cfd_set_step_global", "b200cfd_pack_columns", "b200cfd_unpack_columns",
 ]
 
 _lib = None
@@ -95,6 +97,14 @@ def load():
     lib.b200cfd_k_apply_ibm.argtypes = [vp, vp, vp, vp, dbl, vp]
     lib.b200cfd_k_clean_divergence.argtypes = [vp, vp, vp, i32, i32, vp, vp]
     lib.b200cfd_k_predictor.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, i64, dbl, vp]
+    lib.b200cfd_required_halo.argtypes = [C.POINTER(Config), C.POINTER(i32), C.POINTER(i32)]
+    lib.b200cfd_step_begin.argtypes = [vp, i32, vp]
+    lib.b200cfd_step_end.argtypes = [vp, vp, i32, vp]
+    lib.b200cfd_reduction_ptr.argtypes = [vp]
+    lib.b200cfd_reduction_ptr.restype = vp
+    lib.b200cfd_set_step_global.argtypes = [vp, i64, dbl, dbl, vp]
+    lib.b200cfd_pack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
+    lib.b200cfd_unpack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
     _lib = lib
     return lib
 

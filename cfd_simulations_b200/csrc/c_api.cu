@@ -32,6 +32,7 @@ struct b200cfd_handle {
     int ring_cap = 8192;
     void *ua = nullptr, *va = nullptr, *psi[2] = {nullptr, nullptr}, *tmp = nullptr;
     double* ke_part = nullptr;
+    double* red = nullptr;            // this slab's reduction vector (RED_N doubles)
     unsigned long long* cnt_part = nullptr;
     int n_part = 0;
     // caller-owned (bound) device memory
@@ -44,6 +45,7 @@ struct b200cfd_handle {
     // cached CUDA graph of one time step
     cudaStream_t cap_stream = nullptr;
     cudaGraphExec_t step_graph = nullptr;
+    cudaGraphExec_t begin_graph = nullptr;   // the step without its closing kernel (multi-GPU: all_gather in between)
     PoissonTB* tb = nullptr;          // temporally blocked Poisson state (tensor maps, scratch)
     int gpu_launches = 0;             // kernels enqueued by the last b200cfd_step call (per step)
     // optional per-phase profiling (CUDA events between the kernels of a step; non-graph path only)
@@ -64,9 +66,10 @@ static int fail(b200cfd_handle* h, int code, const char* fmt, ...) {
 #define CU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(h, B200CFD_ECUDA, "%s: %s", #call, cudaGetErrorString(e_)); } while (0)
 #define CHECK_LAUNCH(h) do { cudaError_t e_ = cudaPeekAtLastError(); if (e_ != cudaSuccess) return fail(h, B200CFD_ECUDA, "kernel launch: %s", cudaGetErrorString(e_)); } while (0)
 
-static Geom make_geom(int ny, int nx, long long pitch, double dx, double dy, int jg0, int nxg) {
+static Geom make_geom(int ny, int nx, long long pitch, double dx, double dy, int jg0, int nxg, int own0 = 0, int own1 = -1) {
     Geom g;
     g.ny = ny; g.nx = nx; g.pitch = pitch; g.jg0 = jg0; g.nxg = nxg;
+    g.own0 = own0; g.own1 = own1 < 0 ? nx : own1;
     g.dx = dx; g.dy = dy;
     g.hdx = 0.5 / dx; g.hdy = 0.5 / dy;                 // v5.py:131-132,182-183,193-194
     g.qdx = 0.5 * g.hdx; g.qdy = 0.5 * g.hdy;           // v5.py:137-138
@@ -110,7 +113,9 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     h->n_sm = prop.multiProcessorCount;
     const int nxg = cfg->nranks > 1 ? cfg->nx_global : cfg->nx;
     const int jg0 = cfg->nranks > 1 ? cfg->x_offset : 0;
-    h->g = make_geom(cfg->ny, cfg->nx, cfg->nx, cfg->dx, cfg->dy, jg0, nxg);
+    if (cfg->halo_left < 0 || cfg->halo_right < 0 || cfg->halo_left + cfg->halo_right >= cfg->nx) { delete h; return fail(nullptr, B200CFD_EINVAL, "bad halo widths %d/%d for nx=%d", cfg->halo_left, cfg->halo_right, cfg->nx); }
+    if (jg0 < 0 || jg0 + cfg->nx > nxg) { delete h; return fail(nullptr, B200CFD_EINVAL, "slab [%d,%d) outside the global grid of %d columns", jg0, jg0 + cfg->nx, nxg); }
+    h->g = make_geom(cfg->ny, cfg->nx, cfg->nx, cfg->dx, cfg->dy, jg0, nxg, cfg->halo_left, cfg->nx - cfg->halo_right);
     const bool f32 = cfg->dtype == B200CFD_F32;
     h->phys.nu_eff = f32 ? (double)(float)((float)cfg->nu + (float)cfg->av) : cfg->nu + cfg->av;   // v5.py:388 in the field dtype
     h->phys.V_inf = cfg->V_inf; h->phys.y_max = cfg->y_max; h->phys.max_velocity = cfg->max_velocity;
@@ -133,6 +138,8 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     h->n_part = finalize_num_partials(h->g);
     CUC(cudaMalloc(&h->ke_part, sizeof(double) * h->n_part));
     CUC(cudaMalloc(&h->cnt_part, sizeof(unsigned long long) * (h->n_part > 4 ? h->n_part : 4)));
+    CUC(cudaMalloc(&h->red, sizeof(double) * RED_N));
+    CUC(cudaMemset(h->red, 0, sizeof(double) * RED_N));
     CUC(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
     launch_ctl_init(h->ctl, h->cp, 0, 0, nullptr);
     CUC(cudaDeviceSynchronize());
@@ -145,10 +152,11 @@ int b200cfd_destroy(b200cfd_handle* h) {
     if (!h) return B200CFD_OK;
     cudaSetDevice(h->device);
     if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
+    if (h->begin_graph) cudaGraphExecDestroy(h->begin_graph);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->tb) poisson_tb_destroy(h->tb);
     cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
-    cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part);
+    cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part); cudaFree(h->red);
     delete h;
     return B200CFD_OK;
 }
@@ -164,6 +172,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
     h->ibm = ibm_mask; h->mask = cylinder_mask; h->y = y;
     h->bound = true;
     if (h->step_graph) { cudaGraphExecDestroy(h->step_graph); h->step_graph = nullptr; }
+    if (h->begin_graph) { cudaGraphExecDestroy(h->begin_graph); h->begin_graph = nullptr; }
     return B200CFD_OK;
 }
 
@@ -261,7 +270,7 @@ static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& 
     ++idx;
 }
 
-static int enqueue_step(b200cfd_handle* h, cudaStream_t s) {
+static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     const b200cfd_config& c = h->cfg;
     const int dt = c.dtype;
     int nl = 0, pi = 0;
@@ -278,7 +287,8 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s) {
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
     launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s); ++nl;
     prof_mark(h, "finalize", s, pi);
-    launch_ctl_end_step(h->ctl, h->cp, h->ke_part, h->cnt_part, h->n_part, h->ring, h->ring_cap, s); ++nl;
+    launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part, h->red, s); ++nl;
+    if (close) { launch_ctl_end_step(h->ctl, h->cp, h->red, 1, h->ring, h->ring_cap, s); ++nl; }
     prof_mark(h, "ctl", s, pi);
     if (h->profiling) ++h->prof_steps;
     return nl;
@@ -317,6 +327,88 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
         CHECK_LAUNCH(h);
     }
     h->step += n_steps;
+    return B200CFD_OK;
+}
+
+// ---- multi-GPU (x-slab) stepping: begin = the whole step except its closing kernel; the caller all_gathers the
+// RED_N-double reduction vectors of all slabs; end = closing kernel on the gathered vectors.
+int b200cfd_step_begin(b200cfd_handle* h, int use_graph, void* stream) {
+    if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU(h, cudaSetDevice(h->device));
+    if (h->cfg.nranks > 1 && !(h->cfg.poisson_mode == B200CFD_POISSON_AS_EXECUTED && h->cfg.omega == 1.0))
+        return fail(h, B200CFD_EINVAL, "slab-decomposed stepping supports poisson_mode as_executed only (iterated solves need a halo exchange per iteration: use b200cfd_poisson with pack/unpack_columns)");
+    if (use_graph) {
+        if (!h->begin_graph) {
+            cudaGraph_t graph = nullptr;
+            CU(h, cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+            h->gpu_launches = enqueue_step(h, h->cap_stream, false) + 1;
+            cudaError_t e = cudaStreamEndCapture(h->cap_stream, &graph);
+            if (e != cudaSuccess) return fail(h, B200CFD_ECUDA, "graph capture: %s", cudaGetErrorString(e));
+            e = cudaGraphInstantiate(&h->begin_graph, graph, 0);
+            cudaGraphDestroy(graph);
+            if (e != cudaSuccess) { h->begin_graph = nullptr; return fail(h, B200CFD_ECUDA, "graph instantiate: %s", cudaGetErrorString(e)); }
+        }
+        CU(h, cudaGraphLaunch(h->begin_graph, s));
+    } else {
+        h->gpu_launches = enqueue_step(h, s, false) + 1;
+        CHECK_LAUNCH(h);
+    }
+    return B200CFD_OK;
+}
+int b200cfd_step_end(b200cfd_handle* h, const double* gathered, int nranks, void* stream) {
+    if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");
+    if (nranks < 1) return fail(h, B200CFD_EINVAL, "nranks < 1");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU(h, cudaSetDevice(h->device));
+    launch_ctl_end_step(h->ctl, h->cp, gathered ? gathered : h->red, gathered ? nranks : 1, h->ring, h->ring_cap, s);
+    CHECK_LAUNCH(h);
+    h->step += 1;
+    return B200CFD_OK;
+}
+void* b200cfd_reduction_ptr(b200cfd_handle* h) { return h ? (void*)h->red : nullptr; }
+int b200cfd_reduction_len(void) { return RED_N; }
+// set_step for slabs: the caller supplies the GLOBAL post-clip maxima adaptive_time_step needs (v5.py:322)
+int b200cfd_set_step_global(b200cfd_handle* h, int64_t step, double max_abs_u, double max_abs_v, void* stream) {
+    if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU(h, cudaSetDevice(h->device));
+    unsigned long long bits[2];
+    memcpy(&bits[0], &max_abs_u, 8); memcpy(&bits[1], &max_abs_v, 8);
+    CU(h, cudaMemcpyAsync(&h->ctl->max_u, &bits[0], 8, cudaMemcpyHostToDevice, s));
+    CU(h, cudaMemcpyAsync(&h->ctl->max_v, &bits[1], 8, cudaMemcpyHostToDevice, s));
+    CU(h, cudaStreamSynchronize(s));
+    launch_ctl_init(h->ctl, h->cp, (long long)step, 1, s);
+    CHECK_LAUNCH(h);
+    h->step = step;
+    return B200CFD_OK;
+}
+int b200cfd_pack_columns(b200cfd_handle* h, const void* field, int j0, int ncols, void* buf, void* stream) {
+    if (!h || !field || !buf) return fail(h, B200CFD_EINVAL, "null argument");
+    if (j0 < 0 || ncols < 0 || j0 + ncols > h->g.nx) return fail(h, B200CFD_EINVAL, "columns [%d,%d) outside the slab", j0, j0 + ncols);
+    CU(h, cudaSetDevice(h->device));
+    launch_pack_columns(h->es, h->g, field, j0, ncols, buf, (cudaStream_t)stream);
+    CHECK_LAUNCH(h);
+    return B200CFD_OK;
+}
+int b200cfd_unpack_columns(b200cfd_handle* h, void* field, int j0, int ncols, const void* buf, void* stream) {
+    if (!h || !field || !buf) return fail(h, B200CFD_EINVAL, "null argument");
+    if (j0 < 0 || ncols < 0 || j0 + ncols > h->g.nx) return fail(h, B200CFD_EINVAL, "columns [%d,%d) outside the slab", j0, j0 + ncols);
+    CU(h, cudaSetDevice(h->device));
+    launch_unpack_columns(h->es, h->g, field, j0, ncols, buf, (cudaStream_t)stream);
+    CHECK_LAUNCH(h);
+    return B200CFD_OK;
+}
+// Halo widths (columns) a slab needs so that ONE exchange of u, v per time step suffices: everything
+// else of the step is recomputed redundantly in the halo.  Left = 2 x the horizontal apron of the lexicographic
+// sweep + the stencil radii of the other phases; right = the stencil radii.  No device needed.
+int b200cfd_required_halo(const b200cfd_config* cfg, int* left, int* right) {
+    if (!cfg || !left || !right || !(cfg->dx > 0) || !(cfg->dy > 0)) return B200CFD_EINVAL;
+    Geom g = make_geom(cfg->ny, cfg->nx, cfg->nx, cfg->dx, cfg->dy, 0, cfg->nx);
+    CleanPlan cp = clean_plan(g, cfg->dtype, 148);
+    const int iters = cfg->clean_iters > 0 ? cfg->clean_iters : 0;
+    *left = iters * (cp.apron_h + 3) + 8;
+    *right = 3 * iters + 8;
     return B200CFD_OK;
 }
 

@@ -13,6 +13,8 @@ struct Geom {
     int ny, nx;          // local array shape
     long long pitch;     // row stride in elements
     int jg0, nxg;        // global column of local column 0, global nx (x-slab decomposition)
+    int own0, own1;      // local columns [own0, own1) are OWNED by this slab; the rest are halo columns that are
+                         // recomputed redundantly (results there are never reduced, never sent)
     double dx, dy;
     double hdx, hdy;     // 0.5/dx, 0.5/dy            (divergence / gradient / SUPG dx_inv)
     double qdx, qdy;     // 0.5*hdx, 0.5*hdy          (SUPG first derivative, v5.py:137-138)
@@ -45,7 +47,12 @@ struct StepCtl {
     int pois_done;                    // tolerance reached -> later launches exit immediately
     unsigned int pois_blocks_done;    // last-block election counter
     unsigned int pad1;
+    double energy_sum, energy_cnt;    // global sum / count of the finite 0.5(u^2+v^2) values of this step
 };
+
+// Per-rank reduction vector exchanged between slabs at the end of a step (all_gather of RED_N doubles per rank).
+enum { RED_MAX_DIV_PRE = 0, RED_MAX_GRAD, RED_MAX_DIV_POST, RED_MAX_VORT, RED_MAX_U, RED_MAX_V, RED_POIS_CHANGE,
+       RED_NONFINITE, RED_ENERGY_SUM, RED_ENERGY_CNT, RED_N = 16 };
 
 struct StepScalars {   // must match b200cfd_step_scalars (12 doubles)
     double dt, max_div_pre, max_grad_phi, max_div_post, max_vorticity, mean_energy, max_abs_u, max_abs_v,

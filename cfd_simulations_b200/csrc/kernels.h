@@ -46,9 +46,13 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
                      double* ke_partials, unsigned long long* cnt_partials, cudaStream_t s);
 int finalize_num_partials(const Geom& g);
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s);
-void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* ke_partials,
-                         const unsigned long long* cnt_partials, int n_partials, StepScalars* ring, int ring_cap,
-                         cudaStream_t s);
+void launch_ctl_reduce_local(const StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
+                             int n_partials, double* red, cudaStream_t s);
+void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
+                         int ring_cap, cudaStream_t s);
+// ---- x-slab halos: strided columns <-> contiguous buffer [ny][ncols] (halo.cu) -------------------
+void launch_pack_columns(int es, const Geom& g, const void* field, int j0, int ncols, void* buf, cudaStream_t s);
+void launch_unpack_columns(int es, const Geom& g, void* field, int j0, int ncols, const void* buf, cudaStream_t s);
 void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s);
 void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, StepCtl* ctl, cudaStream_t s);
 

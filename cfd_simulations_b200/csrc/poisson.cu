@@ -32,7 +32,7 @@ k_rbgs_color(Geom g, T* __restrict__ phi, const T* __restrict__ div, const uint8
             const double old = ldp(phi, k);
             double pn = (g.ax * (ldp(phi, k + 1) + ldp(phi, k - 1)) + g.ay * (ldp(phi, k + g.pitch) + ldp(phi, k - g.pitch)) - rhs) * g.dinv;
             if (omega != 1.0) pn = old + omega * (pn - old);
-            ch = fabs(pn - old);
+            if (j >= g.own0 && j < g.own1) ch = fabs(pn - old);
             phi[k] = (T)pn;
         }
     }
@@ -126,12 +126,9 @@ k_div_rb1(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint
                 ch = fabs(p);
             }
         }
-        const bool halo = (j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg);
-        if (!halo) {
-            phi[k] = (T)p;
-            if (div_out) div_out[k] = (T)D;
-        }
-        dabs = fabs(D);
+        phi[k] = (T)p;
+        if (div_out) div_out[k] = (T)D;
+        if (j >= g.own0 && j < g.own1) dabs = fabs(D); else ch = 0.0;
     }
     if (ctl) {
         block_atomic_max(dabs, &ctl->max_div_pre);

@@ -234,11 +234,13 @@ k_predictor(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict
     const long long k = i * g.pitch + j;
     const bool wall = (i == 0 || i == g.ny - 1);
     const bool inflow = (jg == 0), outflow = (jg == g.nxg - 1);
-    if (!inflow && !outflow && (j == 0 || j == g.nx - 1)) return;   // slab halo column
+    const bool ledge = !inflow && !outflow && (j == 0 || j == g.nx - 1);   // outermost halo column of a slab: no stencil
     const double dt = ctl->dt, fs = ctl->fs;
     double ru, rv, tau_o = 0.0;
     if (wall) {
         ru = 0.0; rv = 0.0;
+    } else if (ledge) {
+        ru = ld(u, k); rv = ld(v, k);
     } else if (inflow) {
         ru = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase));
         rv = 0.0;
@@ -278,7 +280,7 @@ k_correct(Geom g, StepCtl* __restrict__ ctl, const T* __restrict__ us, const T* 
         }
         u[k] = (T)axmy<T>(ld(us, k), dt, gx);
         v[k] = (T)axmy<T>(ld(vs, k), dt, gy);
-        gm = sqrt(Rnd<T>::r(Rnd<T>::r(gx * gx) + Rnd<T>::r(gy * gy)));
+        if (j >= g.own0 && j < g.own1) gm = sqrt(Rnd<T>::r(Rnd<T>::r(gx * gx) + Rnd<T>::r(gy * gy)));
     }
     block_atomic_max(gm, &ctl->max_grad);
 }
@@ -316,14 +318,15 @@ k_finalize(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, 
     const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
     double dmax = 0.0, wmax = 0.0, e = 0.0, mu = 0.0, mv = 0.0;
     unsigned cnt = 0, bad = 0;
-    const bool own = i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg));
-    if (own) {
+    // every local cell is computed (halo columns redundantly); only OWNED columns enter the reductions
+    const bool own = i < g.ny && j >= g.own0 && j < g.own1;
+    if (i < g.ny && j < g.nx) {
         const long long k = i * g.pitch + j;
         double fu, fv;
         bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j, fu, fv);
         if (is_interior(g, i, j)) {
-            dmax = fabs(Rnd<T>::r((ld(ua, k + 1) - ld(ua, k - 1)) * g.hdx + (ld(va, k + g.pitch) - ld(va, k - g.pitch)) * g.hdy));
-            if (!(mask && mask[k])) {
+            if (own) dmax = fabs(Rnd<T>::r((ld(ua, k + 1) - ld(ua, k - 1)) * g.hdx + (ld(va, k + g.pitch) - ld(va, k - g.pitch)) * g.hdy));
+            if (own && !(mask && mask[k])) {
                 double eu, ev, wu, wv, nu_, nv, su, sv;
                 bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j + 1, eu, ev);
                 bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j - 1, wu, wv);
@@ -335,14 +338,14 @@ k_finalize(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, 
             }
         }
         const double en = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fu * fu) + Rnd<T>::r(fv * fv)));
-        if (en == en) { e = en; cnt = 1; }
-        if (!isfinite(fu) || !isfinite(fv)) bad = 1;
+        if (own && en == en) { e = en; cnt = 1; }
+        if (own && (!isfinite(fu) || !isfinite(fv))) bad = 1;
         const double cu = fmin(fmax(fu, -p.max_velocity), p.max_velocity);
         const double cv = fmin(fmax(fv, -p.max_velocity), p.max_velocity);
         // np.clip propagates NaN; fmin/fmax would drop it
         u[k] = (T)(fu == fu ? cu : fu);
         v[k] = (T)(fv == fv ? cv : fv);
-        mu = fabs(cu); mv = fabs(cv);
+        if (own) { mu = fabs(cu); mv = fabs(cv); }
     }
     block_atomic_max(dmax, &ctl->max_div_post);
     block_atomic_max(wmax, &ctl->max_vort);
@@ -364,7 +367,7 @@ template <typename T>
 __global__ void k_max_abs2(Geom g, const T* __restrict__ u, const T* __restrict__ v, StepCtl* ctl) {
     const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
     double mu = 0.0, mv = 0.0;
-    if (i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg))) {
+    if (i < g.ny && j >= g.own0 && j < g.own1) {
         mu = fabs(ld(u, i * g.pitch + j)); mv = fabs(ld(v, i * g.pitch + j));
     }
     block_atomic_max(mu, &ctl->max_u);
@@ -379,7 +382,7 @@ k_health(Geom g, const T* __restrict__ u, const T* __restrict__ v, unsigned long
     const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
     double mu = 0.0, mv = 0.0, md = 0.0;
     int bad = 0;
-    if (i < g.ny && j < g.nx && !((j == 0 && g.jg0 > 0) || (j == g.nx - 1 && g.jg0 + g.nx < g.nxg))) {
+    if (i < g.ny && j >= g.own0 && j < g.own1) {
         const long long k = i * g.pitch + j;
         const double a = ld(u, k), b = ld(v, k);
         bad = !isfinite(a) || !isfinite(b);
@@ -430,9 +433,10 @@ __global__ void k_ctl_init(StepCtl* c, CtlParams cp, long long step, int use_mea
 
 __global__ void k_ctl_zero_max(StepCtl* c) { if (!threadIdx.x && !blockIdx.x) { c->max_u = 0ull; c->max_v = 0ull; } }
 
-// closes a step: fixed-order sum of the energy partials, ring record, next step's dt / ramps
-__global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
-                               const unsigned long long* __restrict__ cnt_part, int n_part, StepScalars* ring, int cap) {
+// End of a step, part 1: fold this slab's running maxima and the fixed-order sum of its energy partials into the
+// reduction vector red[RED_N] (what the slabs all_gather; on one GPU part 2 reads it directly).
+__global__ void k_ctl_reduce_local(const StepCtl* __restrict__ c, const double* __restrict__ ke_part,
+                                   const unsigned long long* __restrict__ cnt_part, int n_part, double* __restrict__ red) {
     __shared__ double s_e[256];
     __shared__ unsigned long long s_c[256];
     double e = 0.0; unsigned long long n = 0;
@@ -444,18 +448,43 @@ __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restric
         __syncthreads();
     }
     if (threadIdx.x) return;
+    red[RED_MAX_DIV_PRE] = bits_to_double(c->max_div_pre);
+    red[RED_MAX_GRAD] = bits_to_double(c->max_grad);
+    red[RED_MAX_DIV_POST] = bits_to_double(c->max_div_post);
+    red[RED_MAX_VORT] = bits_to_double(c->max_vort);
+    red[RED_MAX_U] = bits_to_double(c->max_u);
+    red[RED_MAX_V] = bits_to_double(c->max_v);
+    red[RED_POIS_CHANGE] = c->pois_last;
+    red[RED_NONFINITE] = (double)c->nonfinite;
+    red[RED_ENERGY_SUM] = s_e[0];
+    red[RED_ENERGY_CNT] = (double)s_c[0];
+    for (int k = RED_ENERGY_CNT + 1; k < RED_N; ++k) red[k] = 0.0;
+}
+
+// End of a step, part 2: combine the reduction vectors of all slabs (max is exact and order independent; the energy sum
+// is taken in rank order), write the ring record, prepare the next step's dt / ramps (adaptive_time_step, v5.py:316-326).
+__global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ gathered, int nranks,
+                               StepScalars* ring, int cap) {
+    if (threadIdx.x || blockIdx.x) return;
+    double m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    double es = 0.0, ec = 0.0;
+    for (int r = 0; r < nranks; ++r) {
+        const double* v = gathered + (size_t)r * RED_N;
+        for (int k = 0; k < 8; ++k) m[k] = fmax(m[k], v[k]);
+        es += v[RED_ENERGY_SUM]; ec += v[RED_ENERGY_CNT];
+    }
     StepScalars r;
     r.dt = c->dt;
-    r.max_div_pre = bits_to_double(c->max_div_pre);
-    r.max_grad_phi = bits_to_double(c->max_grad);
-    r.max_div_post = bits_to_double(c->max_div_post);
-    r.max_vorticity = bits_to_double(c->max_vort);
-    r.mean_energy = s_c[0] ? s_e[0] / (double)s_c[0] : __longlong_as_double(0x7ff8000000000000ll);
-    r.max_abs_u = bits_to_double(c->max_u);
-    r.max_abs_v = bits_to_double(c->max_v);
+    r.max_div_pre = m[RED_MAX_DIV_PRE];
+    r.max_grad_phi = m[RED_MAX_GRAD];
+    r.max_div_post = m[RED_MAX_DIV_POST];
+    r.max_vorticity = m[RED_MAX_VORT];
+    r.mean_energy = ec > 0.0 ? es / ec : __longlong_as_double(0x7ff8000000000000ll);
+    r.max_abs_u = m[RED_MAX_U];
+    r.max_abs_v = m[RED_MAX_V];
     r.poisson_iters = (double)c->pois_iters;
-    r.poisson_change = c->pois_last;
-    r.nonfinite = (double)c->nonfinite;
+    r.poisson_change = m[RED_POIS_CHANGE];
+    r.nonfinite = m[RED_NONFINITE];
     r.step = (double)c->step;
     ring[(int)(c->step % cap)] = r;
     c->in_max_u = r.max_abs_u; c->in_max_v = r.max_abs_v;
@@ -540,10 +569,13 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s) {
     k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max);
 }
-void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* ke_partials,
-                         const unsigned long long* cnt_partials, int n_partials, StepScalars* ring, int ring_cap,
-                         cudaStream_t s) {
-    k_ctl_end_step<<<1, 256, 0, s>>>(ctl, cp, ke_partials, cnt_partials, n_partials, ring, ring_cap);
+void launch_ctl_reduce_local(const StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
+                             int n_partials, double* red, cudaStream_t s) {
+    k_ctl_reduce_local<<<1, 256, 0, s>>>(ctl, ke_partials, cnt_partials, n_partials, red);
+}
+void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
+                         int ring_cap, cudaStream_t s) {
+    k_ctl_end_step<<<1, 32, 0, s>>>(ctl, cp, gathered, nranks, ring, ring_cap);
 }
 void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s) {
     cudaMemsetAsync(out4, 0, 4 * sizeof(unsigned long long), s);

@@ -9,9 +9,11 @@ from __future__ import annotations
 import numpy as np
 
 
-def setup_grid(cfg):
-    """v5.py:269-273."""
+def setup_grid(cfg, cols=None):
+    """v5.py:269-273.  cols = (first global column, number of columns) restricts x to one x-slab."""
     x = np.linspace(cfg.x_min, cfg.x_max, cfg.nx)
+    if cols is not None:
+        x = x[cols[0]:cols[0] + cols[1]]
     y = np.linspace(cfg.y_min, cfg.y_max, cfg.ny)
     X, Y = np.meshgrid(x, y, indexing="xy")
     return x, y, X, Y
@@ -43,3 +45,36 @@ def initialize_potential_flow(cfg, X, Y, dist, ibm_mask, dtype):
     u = np.where(far, u_far, u_near).astype(dtype)
     v = np.where(far, v_far, 0.0).astype(dtype)
     return np.ascontiguousarray(u), np.ascontiguousarray(v)
+
+
+def setup_on_device(cfg, device, cols=None):
+    """The same three setup steps (v5.py:269-314) evaluated with torch on the GPU, for grids where the host arrays
+    would not fit comfortably (16384^2 per slab).  One-time setup, not part of the time step; transcendental
+    functions may differ from NumPy's in the last ulp, so parity tests against the oracle use the host path.
+    Returns x, y (host float64), cylinder_mask (uint8), ibm_mask (float64), u0, v0 (field dtype) as device tensors."""
+    import torch
+    x = np.linspace(cfg.x_min, cfg.x_max, cfg.nx)
+    if cols is not None:
+        x = x[cols[0]:cols[0] + cols[1]]
+    y = np.linspace(cfg.y_min, cfg.y_max, cfg.ny)
+    X = torch.from_numpy(np.ascontiguousarray(x)).to(device)[None, :]
+    Y = torch.from_numpy(y).to(device)[:, None]
+    x_c, y_c = cfg.cylinder_center
+    R = cfg.R_cylinder
+    dist = torch.sqrt((X - x_c) ** 2 + (Y - y_c) ** 2)
+    mask = (dist <= R).to(torch.uint8)
+    sigma = 2 * cfg.dx
+    ibm = torch.exp(-((dist - R) / sigma) ** 2)
+    zero = torch.zeros((), dtype=torch.float64, device=device)
+    one = torch.ones((), dtype=torch.float64, device=device)
+    ibm = torch.where(dist < R, one, torch.where(dist < R + 5 * cfg.dx, ibm, zero))
+    far = dist > R + 4 * cfg.dx
+    theta2 = 2 * torch.atan2(Y - y_c, X - x_c)
+    factor = (R / dist) ** 2
+    om = 1 - ibm
+    tdt = torch.float32 if cfg.field_dtype == np.float32 else torch.float64
+    u = torch.where(far, cfg.V_inf * (1 - factor * torch.cos(theta2)) * om,
+                    cfg.V_inf * torch.clamp(((dist - R) / (4 * cfg.dx)) ** 2, max=1.0) * om).to(tdt).contiguous()
+    v = torch.where(far, -cfg.V_inf * factor * torch.sin(theta2) * om, zero).to(tdt).contiguous()
+    del dist, far, theta2, factor, om
+    return x, y, mask.contiguous(), ibm.contiguous(), u, v

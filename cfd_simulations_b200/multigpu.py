@@ -1,0 +1,191 @@
+"""x-slab decomposition of the projection time step over the GPUs of one node (one process per GPU).
+
+The reference is single-process; this is the B200-native scaling of its time step.
+
+Design: communication-avoiding slabs.  Rank r owns global columns [x0, x1) and stores [x0 - HL, x1 + HR): HL / HR halo
+columns on interior sides.  Every kernel of the step runs on the whole local array, so halo cells are recomputed
+redundantly and their region of validity shrinks by the stencil radius of each phase; HL, HR (b200cfd_required_halo) are
+chosen so that after a full step all OWNED cells are exact.  Per time step there is therefore exactly
+  * one all_gather of a 16-double reduction vector (max|div|, max|grad phi|, max|vorticity|, energy sum, max|u|,|v| for the
+    adaptive dt, ...) between step_begin and step_end, and
+  * one halo refresh of u and v (pack columns -> NCCL send/recv over NVLink -> unpack),
+and no mid-step exchange.  The left halo is wide (2 x the upstream apron of the lexicographic clean-divergence sweep,
+about 80 columns) because that sweep's dependence runs left-to-right; the right halo is 14 columns.  At 16384 columns
+per slab the redundant work is 0.6 %.
+
+SlabPlan / HaloExchanger are pure host logic (tested on CPU with gloo, world_size 2); the pack/unpack callables the
+product passes in are CUDA kernels behind the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+@dataclass(frozen=True)
+class SlabPlan:
+    """Column ranges of one slab.  All numbers are columns; g = global index, l = local index."""
+    rank: int
+    nranks: int
+    nx_global: int
+    x0: int            # first owned global column
+    x1: int            # one past the last owned global column
+    halo_left: int     # halo columns stored left of x0 (0 on rank 0)
+    halo_right: int    # halo columns stored right of x1 (0 on the last rank)
+    send_left: int     # columns the LEFT neighbour needs from me  (= its halo_right)
+    send_right: int    # columns the RIGHT neighbour needs from me (= its halo_left)
+
+    @property
+    def x_offset(self):
+        return self.x0 - self.halo_left
+
+    @property
+    def nx_local(self):
+        return (self.x1 - self.x0) + self.halo_left + self.halo_right
+
+    @property
+    def own0(self):
+        return self.halo_left
+
+    @property
+    def own1(self):
+        return self.halo_left + (self.x1 - self.x0)
+
+
+def make_plan(nx_global, nranks, rank, halo_left, halo_right):
+    """Even split of nx_global columns (the first nx_global % nranks slabs get one more)."""
+    if not (0 <= rank < nranks):
+        raise ValueError(f"rank {rank} outside [0, {nranks})")
+    base, rem = divmod(nx_global, nranks)
+    x0 = rank * base + min(rank, rem)
+    x1 = x0 + base + (1 if rank < rem else 0)
+    if nranks > 1 and base < max(halo_left, halo_right):
+        raise ValueError(f"slabs of {base} columns are narrower than the halo ({halo_left}/{halo_right}): use fewer ranks")
+    hl = halo_left if rank > 0 else 0
+    hr = halo_right if rank < nranks - 1 else 0
+    return SlabPlan(rank, nranks, nx_global, x0, x1, hl, hr,
+                    send_left=halo_right if rank > 0 else 0, send_right=halo_left if rank < nranks - 1 else 0)
+
+
+class HaloExchanger:
+    """Refreshes the halo columns of a list of fields with one batched send/recv per neighbour.
+
+    pack(field, j0, ncols, out2d) / unpack(field, j0, ncols, in2d) move field[:, j0:j0+ncols] to / from a contiguous
+    (ny, ncols) buffer; buffers are allocated once with `alloc(shape)` on the device the backend communicates from."""
+
+    def __init__(self, plan: SlabPlan, ny, nfields, alloc, pack, unpack, group=None):
+        self.plan, self.ny, self.nf, self.pack, self.unpack, self.group = plan, ny, nfields, pack, unpack, group
+        p = plan
+        mk = lambda n: alloc((nfields, ny, n)) if n > 0 else None
+        self.sbuf_l, self.sbuf_r = mk(p.send_left), mk(p.send_right)
+        self.rbuf_l, self.rbuf_r = mk(p.halo_left), mk(p.halo_right)
+        self.bytes_per_exchange = sum(b.numel() * b.element_size() for b in (self.sbuf_l, self.sbuf_r) if b is not None)
+
+    def exchange(self, fields):
+        p = self.plan
+        assert len(fields) == self.nf
+        ops = []
+        # post receives first, then pack and send
+        if self.rbuf_l is not None:
+            ops.append(dist.P2POp(dist.irecv, self.rbuf_l, p.rank - 1, self.group))
+        if self.rbuf_r is not None:
+            ops.append(dist.P2POp(dist.irecv, self.rbuf_r, p.rank + 1, self.group))
+        for k, f in enumerate(fields):
+            if self.sbuf_l is not None:
+                self.pack(f, p.own0, p.send_left, self.sbuf_l[k])
+            if self.sbuf_r is not None:
+                self.pack(f, p.own1 - p.send_right, p.send_right, self.sbuf_r[k])
+        if self.sbuf_l is not None:
+            ops.append(dist.P2POp(dist.isend, self.sbuf_l, p.rank - 1, self.group))
+        if self.sbuf_r is not None:
+            ops.append(dist.P2POp(dist.isend, self.sbuf_r, p.rank + 1, self.group))
+        if not ops:
+            return
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        for k, f in enumerate(fields):
+            if self.rbuf_l is not None:
+                self.unpack(f, 0, p.halo_left, self.rbuf_l[k])
+            if self.rbuf_r is not None:
+                self.unpack(f, p.own1, p.halo_right, self.rbuf_r[k])
+
+
+class _DevPtr:
+    """Expose a raw device pointer to torch (zero-copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr, n, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def device_view(ptr, n, device):
+    return torch.as_tensor(_DevPtr(ptr, n), device=device)
+
+
+class LocalSlabs:
+    """All slabs of a decomposition stepped in lockstep inside ONE process on ONE GPU (no NCCL): the all_gather is a
+    device copy and the halo refresh packs from one slab and unpacks into its neighbour.  Same kernels, same halo
+    widths, same reduction path as the multi-process run — it makes the decomposition numerics testable on a
+    single-GPU box (SURVEY §4 "virtual slabs") and is what tests/test_gpu_parity.py uses."""
+
+    def __init__(self, config, nslabs, device=0, **kw):
+        from .solver import OptimizedTurbulentSolver
+        self.slabs = [OptimizedTurbulentSolver(config, device=device, nranks=nslabs, rank=r, **kw) for r in range(nslabs)]
+        self.config = config
+
+    def advance(self, n_steps):
+        from .solver import _stream_ptr
+        from ._lib import check
+        S = self.slabs
+        for _ in range(n_steps):
+            for s in S:
+                check(s._lib.b200cfd_step_begin(s._h, int(s._use_graph), _stream_ptr(s.device)), s._h)
+            g = torch.stack([s._red for s in S])
+            for s in S:
+                s._gathered.copy_(g)
+                check(s._lib.b200cfd_step_end(s._h, s._gathered.data_ptr(), len(S), _stream_ptr(s.device)), s._h)
+                s._step += 1
+            self.refresh_halos()
+
+    def refresh_halos(self, names=("u", "v")):
+        S = self.slabs
+        for a, b in zip(S[:-1], S[1:]):          # a is the left neighbour of b
+            pa, pb = a.plan, b.plan
+            for k, name in enumerate(names):
+                fa, fb = a._d[name], b._d[name]
+                a._halo.pack(fa, pa.own1 - pa.send_right, pa.send_right, a._halo.sbuf_r[k])
+                b._halo.unpack(fb, 0, pb.halo_left, a._halo.sbuf_r[k])
+                b._halo.pack(fb, pb.own0, pb.send_left, b._halo.sbuf_l[k])
+                a._halo.unpack(fa, pa.own1, pa.halo_right, b._halo.sbuf_l[k])
+
+    def set_step(self, step):
+        S = self.slabs
+        hv = [s._local_health() for s in S]
+        mu, mv = max(h[1] for h in hv), max(h[2] for h in hv)
+        from .solver import _stream_ptr
+        from ._lib import check
+        for s in S:
+            s._sync_scalars()
+            check(s._lib.b200cfd_set_step_global(s._h, int(step), mu, mv, _stream_ptr(s.device)), s._h)
+            s._step = s._fetched = s._first_step = int(step)
+
+    def set_global(self, name, array):
+        for s in self.slabs:
+            p = s.plan
+            s._d[name].copy_(torch.as_tensor(np.ascontiguousarray(array[:, p.x_offset:p.x_offset + p.nx_local]),
+                                             dtype=s._d[name].dtype))
+
+    def gather(self, name):
+        return np.concatenate([s._get(name)[:, s.plan.own0:s.plan.own1] for s in self.slabs], axis=1)
+
+    @property
+    def scalars(self):
+        self.slabs[0]._sync_scalars()
+        return self.slabs[0].scalars
+
+    def close(self):
+        for s in self.slabs:
+            s.close()

@@ -26,7 +26,7 @@ def _stream_ptr(device):
 
 
 def make_c_config(cfg, ny, nx, poisson_mode, cleandiv_mode, omega, clean_iters, rank=0, nranks=1, nx_global=None,
-                  x_offset=0, halo=0):
+                  x_offset=0, halo_left=0, halo_right=0):
     if not cfg.use_fast_pressure:
         poisson_mode = "jacobi"          # v5.py:336: the NumPy Jacobi branch
     return Config(
@@ -39,7 +39,8 @@ def make_c_config(cfg, ny, nx, poisson_mode, cleandiv_mode, omega, clean_iters, 
         cfl_target=float(cfg.cfl_target), dt_min=float(cfg.dt_min), dt_max=float(cfg.dt_max),
         dt_base=float(cfg.dt_base), max_velocity=float(cfg.max_velocity), cs=float(cfg.smagorinsky_constant),
         pressure_tolerance=float(cfg.pressure_tolerance), omega=float(omega),
-        rank=rank, nranks=nranks, nx_global=nx if nx_global is None else nx_global, x_offset=x_offset, halo=halo)
+        rank=rank, nranks=nranks, nx_global=nx if nx_global is None else nx_global, x_offset=x_offset,
+        halo_left=halo_left, halo_right=halo_right)
 
 
 class OptimizedTurbulentSolver:
@@ -51,29 +52,52 @@ class OptimizedTurbulentSolver:
     """
 
     def __init__(self, config, device=0, poisson_mode="as_executed", cleandiv_mode="lexicographic", omega=1.0,
-                 clean_iters=2, use_graph=True):
+                 clean_iters=2, use_graph=True, nranks=1, rank=0, group=None, setup="host"):
+        """nranks > 1: this process holds x-slab `rank` of `nranks` (multigpu.py; torch.distributed must be
+        initialised, NCCL).  setup = "host" (NumPy, bit-identical to the reference's arrays) | "device" (torch on the
+        GPU, for slabs too large for comfortable host setup; p is not allocated)."""
         if not torch.cuda.is_available():
             raise B200CFDError("no CUDA device: cfd_simulations_b200 has no CPU fallback")
         self.config = cfg = config
         self.device = torch.device("cuda", device)
         self._lib = _lib.load()
         self._use_graph = bool(use_graph)
-        # ---- host setup exactly as the reference (v5.py:269-314) ----
-        self.x, self.y, self.X, self.Y = hostsetup.setup_grid(cfg)
-        self.dist, self.cylinder_mask, self.ibm_mask = hostsetup.setup_boundary_masks(cfg, self.X, self.Y)
+        self._nranks, self._rank, self._group = int(nranks), int(rank), group
+        from . import multigpu
+        hl = hr = C.c_int(0)
+        if nranks > 1:
+            hl, hr = C.c_int(0), C.c_int(0)
+            probe = make_c_config(cfg, cfg.ny, cfg.nx, poisson_mode, cleandiv_mode, omega, clean_iters)
+            check(self._lib.b200cfd_required_halo(C.byref(probe), C.byref(hl), C.byref(hr)))
+        self.plan = plan = multigpu.make_plan(cfg.nx, self._nranks, self._rank, hl.value, hr.value)
+        cols = None if nranks == 1 else (plan.x_offset, plan.nx_local)
         npdt = cfg.field_dtype
-        u0, v0 = hostsetup.initialize_potential_flow(cfg, self.X, self.Y, self.dist, self.ibm_mask, npdt)
         tdt = _torch_dtype(npdt)
         dev = self.device
-        z = lambda: torch.zeros((cfg.ny, cfg.nx), dtype=tdt, device=dev)
+        nxl = plan.nx_local
+        z = lambda: torch.zeros((cfg.ny, nxl), dtype=tdt, device=dev)
+        if setup == "device":
+            self.x, self.y, mask_d, ibm_d, u_d, v_d = hostsetup.setup_on_device(cfg, dev, cols)
+            self.X = self.Y = self.dist = self.cylinder_mask = self.ibm_mask = None
+        else:
+            # ---- host setup exactly as the reference (v5.py:269-314) ----
+            self.x, self.y, self.X, self.Y = hostsetup.setup_grid(cfg, cols)
+            self.dist, self.cylinder_mask, self.ibm_mask = hostsetup.setup_boundary_masks(cfg, self.X, self.Y)
+            u0, v0 = hostsetup.initialize_potential_flow(cfg, self.X, self.Y, self.dist, self.ibm_mask, npdt)
+            u_d, v_d = torch.from_numpy(u0).to(dev), torch.from_numpy(v0).to(dev)
+            ibm_d = torch.from_numpy(np.ascontiguousarray(self.ibm_mask, dtype=np.float64)).to(dev)
+            mask_d = torch.from_numpy(np.ascontiguousarray(self.cylinder_mask, dtype=np.uint8)).to(dev)
         self._d = {
-            "u": torch.from_numpy(u0).to(dev), "v": torch.from_numpy(v0).to(dev),
-            "p": z(), "phi": z(), "u_star": z(), "v_star": z(), "div_u_star": z(), "nu_t": z(), "tau_supg": z(),
-            "ibm": torch.from_numpy(np.ascontiguousarray(self.ibm_mask, dtype=np.float64)).to(dev),
-            "mask": torch.from_numpy(np.ascontiguousarray(self.cylinder_mask, dtype=np.uint8)).to(dev),
+            "u": u_d, "v": v_d,
+            "phi": z(), "u_star": z(), "v_star": z(), "div_u_star": z(), "nu_t": z(), "tau_supg": z(),
+            "ibm": ibm_d, "mask": mask_d,
             "y": torch.from_numpy(np.ascontiguousarray(self.y, dtype=np.float64)).to(dev),
         }
-        self._ccfg = make_c_config(cfg, cfg.ny, cfg.nx, poisson_mode, cleandiv_mode, omega, clean_iters)
+        if setup != "device":
+            self._d["p"] = z()           # v5.py:290: allocated, never updated in v3-v5 (SURVEY Q15)
+        self._ccfg = make_c_config(cfg, cfg.ny, nxl, poisson_mode, cleandiv_mode, omega, clean_iters, rank=self._rank,
+                                   nranks=self._nranks, nx_global=cfg.nx, x_offset=plan.x_offset,
+                                   halo_left=plan.halo_left, halo_right=plan.halo_right)
         self._h = C.c_void_p()
         check(self._lib.b200cfd_create(C.byref(self._ccfg), device, C.byref(self._h)))
         d = self._d
@@ -87,6 +111,18 @@ class OptimizedTurbulentSolver:
         self.scalars = []            # list of dicts, one per step (the five logged values + dt ...)
         self._energy_history = []
         self._times = []
+        self._halo = None
+        if self._nranks > 1:
+            n_red = int(self._lib.b200cfd_reduction_len())
+            self._red = multigpu.device_view(self._lib.b200cfd_reduction_ptr(self._h), n_red, dev)
+            self._gathered = torch.zeros((self._nranks, n_red), dtype=torch.float64, device=dev)
+            lib, h = self._lib, self._h
+            sp = lambda: _stream_ptr(dev)
+            self._halo = multigpu.HaloExchanger(
+                plan, cfg.ny, 2, alloc=lambda shape: torch.empty(shape, dtype=tdt, device=dev),
+                pack=lambda f, j0, n, out: check(lib.b200cfd_pack_columns(h, f.data_ptr(), j0, n, out.data_ptr(), sp()), h),
+                unpack=lambda f, j0, n, src: check(lib.b200cfd_unpack_columns(h, f.data_ptr(), j0, n, src.data_ptr(), sp()), h),
+                group=group)
         torch.cuda.synchronize(dev)
 
     # ---- lifetime ----
@@ -109,7 +145,7 @@ class OptimizedTurbulentSolver:
         t = self._d[name]
         t.copy_(torch.as_tensor(np.ascontiguousarray(value), dtype=t.dtype))
         if name in ("u", "v"):
-            check(self._lib.b200cfd_set_step(self._h, self._step, _stream_ptr(self.device)), self._h)
+            self._set_step(self._step)
 
     u = property(lambda s: s._get("u"), lambda s, a: s._set("u", a))
     v = property(lambda s: s._get("v"), lambda s, a: s._set("v", a))
@@ -134,7 +170,16 @@ class OptimizedTurbulentSolver:
         self._sync_scalars()
         self._step = int(value)
         self._fetched = self._first_step = self._step
-        check(self._lib.b200cfd_set_step(self._h, self._step, _stream_ptr(self.device)), self._h)
+        self._set_step(self._step)
+
+    def _set_step(self, step):
+        """self.step = step: re-derive what adaptive_time_step reads (max|u|, max|v| of the current state)."""
+        if self._nranks == 1:
+            check(self._lib.b200cfd_set_step(self._h, step, _stream_ptr(self.device)), self._h)
+        else:
+            hv = self.health()       # global maxima (all_reduce inside)
+            check(self._lib.b200cfd_set_step_global(self._h, step, hv["max_abs_u"], hv["max_abs_v"],
+                                                    _stream_ptr(self.device)), self._h)
 
     @property
     def energy_history(self):
@@ -151,6 +196,8 @@ class OptimizedTurbulentSolver:
         """n x time_step() with no host round trip (state and per-step scalars stay on the device)."""
         cap = 8192
         done = 0
+        if self._nranks > 1:
+            return self._advance_slabs(n_steps, cap)
         while done < n_steps:
             room = cap - (self._step - self._fetched)
             if room <= 0:
@@ -160,6 +207,35 @@ class OptimizedTurbulentSolver:
             check(self._lib.b200cfd_step(self._h, m, int(self._use_graph), _stream_ptr(self.device)), self._h)
             self._step += m
             done += m
+
+    def _advance_slabs(self, n_steps, cap):
+        """Slab stepping: per step one all_gather of the reduction vector and one halo refresh of u, v."""
+        import torch.distributed as dist
+        lib, h, sp = self._lib, self._h, lambda: _stream_ptr(self.device)
+        u, v = self._d["u"], self._d["v"]
+        for _ in range(n_steps):
+            if self._step - self._fetched >= cap:
+                self._sync_scalars()
+            check(lib.b200cfd_step_begin(h, int(self._use_graph), sp()), h)
+            dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+            check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+            self._halo.exchange([u, v])
+            self._step += 1
+
+    def gather(self, name):
+        """Global (ny, nx) array of a field assembled from the owned columns of every slab (all ranks get it)."""
+        loc = self._get(name)[:, self.plan.own0:self.plan.own1]
+        if self._nranks == 1:
+            return loc
+        import torch.distributed as dist
+        parts = [None] * self._nranks
+        dist.all_gather_object(parts, loc, group=self._group)
+        return np.concatenate(parts, axis=1)
+
+    def set_global(self, name, array):
+        """Assign a field from a GLOBAL (ny, nx) host array (each slab takes its columns, halos included)."""
+        p = self.plan
+        self._set(name, np.ascontiguousarray(array[:, p.x_offset:p.x_offset + p.nx_local]))
 
     def time_step(self):
         """v5.py:375-441.  Returns this step's dt (np.float32 when adaptive, as the reference)."""
@@ -171,6 +247,8 @@ class OptimizedTurbulentSolver:
     def time_step_host(self, u_host, v_host, n_steps=1):
         """time_step() on HOST arrays, the way the reference owns its state: uploads u, v, runs n_steps,
         downloads u, v and the last step's scalars (used for the end-to-end measurement)."""
+        if self._nranks > 1:
+            raise B200CFDError("time_step_host is a single-GPU entry point")
         last = StepScalars()
         check(self._lib.b200cfd_step_host(self._h, u_host.ctypes.data, v_host.ctypes.data, n_steps,
                                           int(self._use_graph), C.byref(last), _stream_ptr(self.device)), self._h)
@@ -245,10 +323,19 @@ class OptimizedTurbulentSolver:
         w[self.cylinder_mask] = np.nan
         return w
 
-    def health(self):
-        """Device reductions monitor_simulation_health needs (v5.py:599-613): no field leaves the GPU."""
+    def _local_health(self):
         out = (C.c_double * 4)()
         check(self._lib.b200cfd_health(self._h, C.byref(out), _stream_ptr(self.device)), self._h)
+        return list(out)
+
+    def health(self):
+        """Device reductions monitor_simulation_health needs (v5.py:599-613): no field leaves the GPU."""
+        out = self._local_health()
+        if self._nranks > 1:
+            import torch.distributed as dist
+            t = torch.tensor(list(out), dtype=torch.float64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self._group)
+            out = t.tolist()
         return {"nonfinite": bool(out[0]), "max_abs_u": out[1], "max_abs_v": out[2], "max_div": out[3]}
 
     def profile_steps(self, n_steps):

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200CFD_ABI_VERSION 1
+#define B200CFD_ABI_VERSION 2
 
 enum { B200CFD_F64 = 0, B200CFD_F32 = 1 };
 enum { B200CFD_OK = 0, B200CFD_EINVAL = -1, B200CFD_ECUDA = -2, B200CFD_ENOMEM = -3, B200CFD_ESTATE = -4 };
@@ -54,9 +54,10 @@ typedef struct b200cfd_config {
     double  cfl_target, dt_min, dt_max, dt_base, max_velocity;
     double  cs;                  /* smagorinsky_constant */
     double  pressure_tolerance, omega;
-    /* x-slab decomposition (single GPU: rank 0 of 1, x_offset 0, nx_global = nx, halo 0) */
-    int32_t rank, nranks, nx_global, x_offset, halo;
-    int32_t reserved;
+    /* x-slab decomposition (single GPU: rank 0 of 1, x_offset 0, nx_global = nx, halos 0).
+     * x_offset = global column of local column 0; local columns [halo_left, nx - halo_right) are owned,
+     * the others are halo columns (recomputed redundantly, refreshed by the caller once per step). */
+    int32_t rank, nranks, nx_global, x_offset, halo_left, halo_right;
 } b200cfd_config;
 
 /* Per-step diagnostics, the five values v5.py logs each step (:410,:415,:422,:429,:435) plus dt. */
@@ -101,6 +102,23 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream);
  * pageable host memory), runs n_steps, downloads u,v and the last step's scalars. Synchronises. */
 int b200cfd_step_host(b200cfd_handle* h, void* u_host, void* v_host, int n_steps, int use_graph,
                       b200cfd_step_scalars* last, void* stream);
+
+/* ---- x-slab (multi-GPU) stepping: one process per GPU, one handle per slab -------------------------------
+ * time_step() = step_begin (all kernels of the step except the closing one; fills this slab's reduction vector)
+ *   -> caller all_gathers the b200cfd_reduction_len() doubles at b200cfd_reduction_ptr() over the slabs (NCCL)
+ *   -> step_end(gathered, nranks): global maxima / energy, ring record, next dt (adaptive_time_step v5.py:316-326)
+ *   -> caller refreshes the halo columns of u and v with pack_columns / NCCL send-recv / unpack_columns.
+ * b200cfd_required_halo gives the halo widths for which that single exchange per step is sufficient. */
+int   b200cfd_required_halo(const b200cfd_config* cfg, int* left, int* right);
+int   b200cfd_step_begin(b200cfd_handle* h, int use_graph, void* stream);
+int   b200cfd_step_end(b200cfd_handle* h, const double* gathered_dev, int nranks, void* stream);
+void* b200cfd_reduction_ptr(b200cfd_handle* h);
+int   b200cfd_reduction_len(void);
+/* self.step = step with the GLOBAL max|u|, max|v| of the state (what adaptive_time_step reads). Synchronises. */
+int   b200cfd_set_step_global(b200cfd_handle* h, int64_t step, double max_abs_u, double max_abs_v, void* stream);
+/* field[:, j0:j0+ncols] -> buf[ny][ncols] and back (device pointers; dtype of the handle). */
+int   b200cfd_pack_columns(b200cfd_handle* h, const void* field, int j0, int ncols, void* buf, void* stream);
+int   b200cfd_unpack_columns(b200cfd_handle* h, void* field, int j0, int ncols, const void* buf, void* stream);
 
 /* monitor_simulation_health (v5.py:599-613) reductions over the bound u, v:
  * out4 = {nonfinite (0/1), max|u|, max|v|, max|div(u,v)|}. Synchronises. */

@@ -44,14 +44,14 @@ def measured_peak():
 
 # algorithmic HBM bytes per cell of each phase, fp64 (DESIGN.md "Kernels")
 ALGO_BYTES = {
-    "predictor": 16 + 8 + 16 + 8,        # R u,v,ibm  W u*,v* (+ W tau_supg, a reference attribute)
-    "poisson": 16 + 1 + 8 + 8,           # as executed: R u*,v*,mask  W phi, div_u_star
+    "predictor": 16 + 16 + 8,            # R u,v  W u*,v* (+ W tau_supg, a reference attribute); ibm only in flagged tiles
+    "poisson": 16 + 8 + 8,               # as executed: R u*,v*  W phi, div_u_star; mask only in flagged tiles
     "correct": 24 + 16,                  # R u*,v*,phi  W u,v
     "clean_sweep_1": 16 + 8,             # R u,v  W psi (psi_old = 0)
     "clean_apply_1": 24 + 16,            # R psi,u,v  W u,v
     "clean_sweep_2": 16 + 8 + 8,         # R u,v,psi_old  W psi
-    "clean_apply_2": 24 + 16,
-    "finalize": 16 + 8 + 1 + 16,         # R u,v,ibm,mask  W u,v
+    "clean_apply_2": 24 + 16,            # (general path only; the fast path applies it inside finalize)
+    "finalize": 24 + 16,                 # R psi,u,v  W u,v (last correction fused); ibm, mask only in flagged tiles
     "ctl": 0,
 }
 
@@ -293,7 +293,7 @@ def main():
     torch.cuda.set_device(local)
     nx, ny = args.nx, args.ny
     cfg = OptimizedTurbulentConfig(nx=nx, ny=ny, memory_efficient=False)
-    s = OptimizedTurbulentSolver(cfg, device=local)
+    s = OptimizedTurbulentSolver(cfg, device=local, setup="device" if nx * ny > (1 << 25) else "host")
     cells = nx * ny
 
     # ---- device-resident throughput: CUDA-graph replay, CUDA events, working set (10 fp64 fields = 336 MB) > L2

@@ -9,7 +9,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libb200cfd.so"
-SOURCES = ["step_kernels.cu", "poisson.cu", "poisson_tb.cu", "cleandiv.cu", "euler.cu", "halo.cu", "c_api.cu"]
+SOURCES = ["step_kernels.cu", "step_fast.cu", "poisson.cu", "poisson_tb.cu", "cleandiv.cu", "euler.cu", "halo.cu", "c_api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

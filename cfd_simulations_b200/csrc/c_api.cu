@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 #include <string>
 #include <vector>
@@ -34,7 +35,10 @@ struct b200cfd_handle {
     double* ke_part = nullptr;
     double* red = nullptr;            // this slab's reduction vector (RED_N doubles)
     unsigned long long* cnt_part = nullptr;
-    int n_part = 0;
+    int n_part = 0;                   // capacity of the partial arrays
+    int n_part_used = 0;              // blocks of the finalize kernel in use
+    uint8_t* flags = nullptr;         // tile-flag map of ibm / mask (step_fast.cu)
+    bool fast = false;                // row-marching fast kernels applicable (decided when the fields are bound)
     // caller-owned (bound) device memory
     void *u = nullptr, *v = nullptr, *phi = nullptr, *us = nullptr, *vs = nullptr, *div = nullptr, *tau = nullptr, *nu_t = nullptr;
     const double* ibm = nullptr;
@@ -136,6 +140,9 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     CUC(cudaMemset(h->ua, 0, fb)); CUC(cudaMemset(h->va, 0, fb));
     CUC(cudaMemset(h->psi[0], 0, fb)); CUC(cudaMemset(h->psi[1], 0, fb));   // psi borders must be 0 and are never written
     h->n_part = finalize_num_partials(h->g);
+    { const int nf = finalize_fast_num_partials(h->g, h->n_sm); if (nf > h->n_part) h->n_part = nf; }
+    h->n_part_used = finalize_num_partials(h->g);
+    { int ntx, nty; const int nb = tile_flags_dims(h->g, &ntx, &nty); CUC(cudaMalloc(&h->flags, nb)); CUC(cudaMemset(h->flags, 3, nb)); }
     CUC(cudaMalloc(&h->ke_part, sizeof(double) * h->n_part));
     CUC(cudaMalloc(&h->cnt_part, sizeof(unsigned long long) * (h->n_part > 4 ? h->n_part : 4)));
     CUC(cudaMalloc(&h->red, sizeof(double) * RED_N));
@@ -156,7 +163,7 @@ int b200cfd_destroy(b200cfd_handle* h) {
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->tb) poisson_tb_destroy(h->tb);
     cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
-    cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part); cudaFree(h->red);
+    cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part); cudaFree(h->red); cudaFree(h->flags);
     delete h;
     return B200CFD_OK;
 }
@@ -171,6 +178,14 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
     h->u = u; h->v = v; h->phi = phi; h->us = u_star; h->vs = v_star; h->div = div_u_star; h->tau = tau_supg; h->nu_t = nu_t;
     h->ibm = ibm_mask; h->mask = cylinder_mask; h->y = y;
     h->bound = true;
+    {   // fast kernels: the default configuration on even, 16-byte aligned grids; tile flags of ibm / mask
+        const void* ptrs[] = {u, v, phi, u_star, v_star, div_u_star, tau_supg, h->ua, h->va, h->psi[0], h->psi[1]};
+        h->fast = h->cfg.use_supg && !h->cfg.use_les && fast_path_ok(h->g, ptrs, 11) && !getenv("B200CFD_NO_FAST");
+        CU(h, cudaSetDevice(h->device));
+        launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
+        CU(h, cudaDeviceSynchronize());
+        h->n_part_used = h->fast ? finalize_fast_num_partials(h->g, h->n_sm) : finalize_num_partials(h->g);
+    }
     if (h->step_graph) { cudaGraphExecDestroy(h->step_graph); h->step_graph = nullptr; }
     if (h->begin_graph) { cudaGraphExecDestroy(h->begin_graph); h->begin_graph = nullptr; }
     return B200CFD_OK;
@@ -199,7 +214,12 @@ static int enqueue_step_poisson(b200cfd_handle* h, cudaStream_t s) {
     const size_t fb = (size_t)c.ny * c.nx * h->es;
     int nl = 0;
     if (c.poisson_mode == B200CFD_POISSON_AS_EXECUTED && c.omega == 1.0) {
-        launch_div_rb1(dt, h->g, h->us, h->vs, h->mask, h->phi, h->div, h->phys.inv_cfg_dt, h->ctl, c.pressure_tolerance, s);
+        if (h->fast) {
+            launch_div_rb1_fast(dt, h->g, h->us, h->vs, h->mask, h->phi, h->div, h->phys.inv_cfg_dt, h->ctl, h->flags, h->n_sm, s);
+            launch_rb1_close(h->ctl, c.pressure_tolerance, s);
+        } else {
+            launch_div_rb1(dt, h->g, h->us, h->vs, h->mask, h->phi, h->div, h->phys.inv_cfg_dt, h->ctl, c.pressure_tolerance, s);
+        }
         return 2;
     }
     void* div = h->div ? h->div : h->tmp;   // tmp doubles as div scratch when the caller does not want div_u_star
@@ -227,7 +247,8 @@ static int enqueue_step_poisson(b200cfd_handle* h, cudaStream_t s) {
 }
 
 static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& idx);
-static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, int mode, cudaStream_t s, void** last_psi, bool in_step = false) {
+static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, int mode, cudaStream_t s, void** last_psi, bool in_step = false,
+                         bool defer_last_apply = false) {
     const int dt = h->cfg.dtype;
     const size_t fb = (size_t)h->cfg.ny * h->cfg.nx * h->es;
     int nl = 0;
@@ -251,9 +272,11 @@ static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, in
             int pi = 0;
             launch_clean_sweep(dt, h->g, h->clean, u, v, po, pn, s);
             if (in_step) prof_mark(h, it == 0 ? "clean_sweep_1" : "clean_sweep_2", s, pi);
-            launch_clean_apply(dt, h->g, u, v, pn, s);
-            if (in_step) prof_mark(h, it == 0 ? "clean_apply_1" : "clean_apply_2", s, pi);
-            nl += 2;
+            if (!(defer_last_apply && it == iterations - 1)) {
+                launch_clean_apply(dt, h->g, u, v, pn, s); ++nl;
+                if (in_step) prof_mark(h, it == 0 ? "clean_apply_1" : "clean_apply_2", s, pi);
+            }
+            ++nl;
             last = pn;
         }
     }
@@ -277,17 +300,24 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     const void* nut = nullptr;
     prof_mark(h, nullptr, s, pi);
     if (c.use_les) { launch_smagorinsky(dt, h->g, h->u, h->v, h->nu_t, c.cs, s); nut = h->nu_t; ++nl; }
-    launch_predictor(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, nut, h->ibm, h->y, s); ++nl;
+    if (h->fast) launch_predictor_fast(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, h->ibm, h->y, h->flags, h->n_sm, s);
+    else launch_predictor(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, nut, h->ibm, h->y, s);
+    ++nl;
     prof_mark(h, "predictor", s, pi);
     nl += enqueue_step_poisson(h, s);
     prof_mark(h, "poisson", s, pi);
     launch_correct(dt, h->g, h->ctl, h->us, h->vs, h->phi, h->ua, h->va, s); ++nl;
     prof_mark(h, "correct", s, pi);
-    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, nullptr, true);
+    // fast path: the last clean-divergence correction u,v -= grad(psi) is applied on the fly by the finalize kernel
+    const bool defer = h->fast && c.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && c.clean_iters > 0;
+    void* last_psi = nullptr;
+    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer);
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
-    launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s); ++nl;
+    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, h->ua, h->va, defer ? last_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
+    else launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s);
+    ++nl;
     prof_mark(h, "finalize", s, pi);
-    launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part, h->red, s); ++nl;
+    launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, s); ++nl;
     if (close) { launch_ctl_end_step(h->ctl, h->cp, h->red, 1, h->ring, h->ring_cap, s); ++nl; }
     prof_mark(h, "ctl", s, pi);
     if (h->profiling) ++h->prof_steps;

@@ -56,6 +56,22 @@ void launch_unpack_columns(int es, const Geom& g, void* field, int j0, int ncols
 void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s);
 void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, StepCtl* ctl, cudaStream_t s);
 
+// ---- row-marching fast kernels (step_fast.cu): SUPG on, LES off, even nx, 16-byte aligned fields ----
+int tile_flags_dims(const Geom& g, int* ntx, int* nty);     // returns ntx * nty (bytes of the flag map)
+void launch_tile_flags(const Geom& g, const double* ibm, const uint8_t* mask, uint8_t* flags, cudaStream_t s);
+bool fast_path_ok(const Geom& g, const void* const* ptrs, int n);
+void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
+                           void* us, void* vs, void* tau_or_null, const double* ibm, const double* y,
+                           const uint8_t* flags, int n_sm, cudaStream_t s);
+void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
+                         void* div_out, double inv_dt, StepCtl* ctl, const uint8_t* flags, int n_sm, cudaStream_t s);
+int finalize_fast_num_partials(const Geom& g, int n_sm);
+void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
+                          const void* psi_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,
+                          const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
+                          int n_sm, cudaStream_t s);
+void launch_rb1_close(StepCtl* ctl, double tol, cudaStream_t s);
+
 // ---- Poisson -----------------------------------------------------------------------------------
 // one red-black colour half-sweep (global colour parity), fused max|dphi|, last block closes the iteration
 void launch_rbgs_color(int dtype, const Geom& g, void* phi, const void* div, const uint8_t* mask, double inv_dt,

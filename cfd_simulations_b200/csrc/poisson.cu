@@ -3,6 +3,7 @@
 // The temporally blocked shared-memory/TMA versions live in poisson_tb.cu; these are the general
 // fallbacks (any shape, any pitch) and the building blocks of the tolerance-terminated mode.
 #include "kernels.h"
+#include "cellmath.cuh"
 
 namespace b200cfd {
 
@@ -84,52 +85,12 @@ __global__ void k_poisson_reset(StepCtl* c) {
 // the four (odd) neighbours evaluated in place from D at those cells.  Masked / border cells stay 0.
 // Also materialises div_u_star (the reference keeps it as an attribute, v5.py:409) and max|div| (v5.py:410).
 template <typename T>
-__device__ __forceinline__ double div_at(const Geom& g, const T* __restrict__ us, const T* __restrict__ vs, int i, int j) {
-    // 0 outside the global interior (compute_divergence_fast leaves the border 0)
-    if (i < 1 || i >= g.ny - 1 || g.jg0 + j < 1 || g.jg0 + j >= g.nxg - 1 || j < 1 || j >= g.nx - 1) return 0.0;
-    const long long k = i * g.pitch + j;
-    return Rnd<T>::r((ldp(us, k + 1) - ldp(us, k - 1)) * g.hdx + (ldp(vs, k + g.pitch) - ldp(vs, k - g.pitch)) * g.hdy);
-}
-template <typename T>
-__device__ __forceinline__ double odd_phi_at(const Geom& g, const T* __restrict__ us, const T* __restrict__ vs,
-                                             const uint8_t* __restrict__ mask, double inv_dt, int i, int j) {
-    // value after the first colour of an odd cell, 0 if it is border / masked
-    if (i < 1 || i >= g.ny - 1 || g.jg0 + j < 1 || g.jg0 + j >= g.nxg - 1) return 0.0;
-    if (mask && mask[i * g.pitch + j]) return 0.0;
-    const double rhs = -div_at<T>(g, us, vs, i, j) * inv_dt;
-    return Rnd<T>::r((g.ax * 0.0 + g.ay * 0.0 - rhs) * g.dinv);
-}
-template <typename T>
 __global__ void __launch_bounds__(PBX* PBY)
 k_div_rb1(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint8_t* __restrict__ mask,
           T* __restrict__ phi, T* __restrict__ div_out, double inv_dt, StepCtl* __restrict__ ctl) {
     const int j = blockIdx.x * PBX + threadIdx.x, i = blockIdx.y * PBY + threadIdx.y;
     double dabs = 0.0, ch = 0.0;
-    // slab halo columns hold no owned cell; columns 1 / nx-2 of a slab need a 2-wide halo of u*, v*
-    if (i < g.ny && j < g.nx) {
-        const long long k = i * g.pitch + j;
-        const int jg = g.jg0 + j;
-        const bool interior = i >= 1 && i < g.ny - 1 && jg >= 1 && jg < g.nxg - 1 && j >= 1 && j < g.nx - 1;
-        double D = 0.0, p = 0.0;
-        if (interior) {
-            D = div_at<T>(g, us, vs, i, j);
-            if (!(mask && mask[k])) {
-                const double rhs = -D * inv_dt;
-                if ((i + jg) & 1) p = (g.ax * 0.0 + g.ay * 0.0 - rhs) * g.dinv;
-                else {
-                    const double pe = odd_phi_at<T>(g, us, vs, mask, inv_dt, i, j + 1);
-                    const double pw = odd_phi_at<T>(g, us, vs, mask, inv_dt, i, j - 1);
-                    const double pn = odd_phi_at<T>(g, us, vs, mask, inv_dt, i + 1, j);
-                    const double ps = odd_phi_at<T>(g, us, vs, mask, inv_dt, i - 1, j);
-                    p = (g.ax * (pe + pw) + g.ay * (pn + ps) - rhs) * g.dinv;
-                }
-                ch = fabs(p);
-            }
-        }
-        phi[k] = (T)p;
-        if (div_out) div_out[k] = (T)D;
-        if (j >= g.own0 && j < g.own1) dabs = fabs(D); else ch = 0.0;
-    }
+    if (i < g.ny && j < g.nx) divrb1_point<T>(g, us, vs, mask, phi, div_out, inv_dt, i, j, dabs, ch);
     if (ctl) {
         block_atomic_max(dabs, &ctl->max_div_pre);
         block_atomic_max(ch, &ctl->pois_change);
@@ -140,6 +101,8 @@ __global__ void k_rb1_close(StepCtl* c, double tol) {
     const double ch = bits_to_double(c->pois_change);
     c->pois_last = ch; c->pois_iters = 1; c->pois_change = 0ull; c->pois_done = ch < tol ? 1 : 0;
 }
+
+void launch_rb1_close(StepCtl* ctl, double tol, cudaStream_t s) { k_rb1_close<<<1, 32, 0, s>>>(ctl, tol); }
 
 static inline dim3 pgrid(const Geom& g) { return dim3((g.nx + PBX - 1) / PBX, (g.ny + PBY - 1) / PBY); }
 static inline dim3 pgrid_color(const Geom& g) { return dim3((g.nx / 2 + 1 + PBX - 1) / PBX, (g.ny + PBY - 1) / PBY); }

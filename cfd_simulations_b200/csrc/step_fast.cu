@@ -1,0 +1,450 @@
+// step_fast.cu — row-marching fast versions of the step kernels for the common case (SUPG on, LES off, even nx,
+// 16-byte aligned fields).  Same arithmetic as the general kernels in step_kernels.cu / poisson.cu (they remain the
+// path for every other configuration), reorganised so that the kernels are HBM-bound instead of issue-bound:
+//   * each thread owns 2 adjacent columns (one 128-bit load / store per row and field) and marches down a chunk of
+//     rows keeping the rows i-1, i, i+1 in registers, so north/south neighbours cost nothing;
+//   * the block reductions (max|div|, max|vorticity|, energy sum, ...) happen once per block, not once per 256 cells;
+//   * the immersed-boundary mask (fp64, 8 B/cell) and the cylinder mask are only read where they are non-trivial:
+//     a tile-flag map (32 columns x 8 rows per flag, built once when the fields are bound) says which tiles contain
+//     ibm > 0 or masked cells (dilated by 2 cells); warps whose tile is flagged, and the few threads that hold a
+//     border column, run the general per-cell code (cellmath.cuh), everything else runs the lean interior path.
+// Reference: python/flow_over_cylinder (Fischer)/v5.py:127-176 (SUPG, convection, Laplacian), :178-226 (divergence,
+// red-black iteration), :349-360 (BC), :228-237 (IBM), :421-438 (diagnostics, clip).
+#include "kernels.h"
+#include "cellmath.cuh"
+
+namespace b200cfd {
+
+#define FT_W 32      // flag tile: columns
+#define FT_H 8       // flag tile: rows
+#define FBT 128      // threads per block of the marching kernels
+#define FCOLS 256    // columns per block (2 per thread)
+
+struct D2 { double x, y; };
+template <typename T> __device__ __forceinline__ D2 ld2(const T* __restrict__ p, long long k);
+template <> __device__ __forceinline__ D2 ld2<double>(const double* __restrict__ p, long long k) {
+    const double2 t = *reinterpret_cast<const double2*>(p + k);
+    return D2{t.x, t.y};
+}
+template <> __device__ __forceinline__ D2 ld2<float>(const float* __restrict__ p, long long k) {
+    const float2 t = *reinterpret_cast<const float2*>(p + k);
+    return D2{(double)t.x, (double)t.y};
+}
+template <typename T> __device__ __forceinline__ void st2(T* __restrict__ p, long long k, double a, double b);
+template <> __device__ __forceinline__ void st2<double>(double* __restrict__ p, long long k, double a, double b) {
+    *reinterpret_cast<double2*>(p + k) = make_double2(a, b);
+}
+template <> __device__ __forceinline__ void st2<float>(float* __restrict__ p, long long k, double a, double b) {
+    *reinterpret_cast<float2*>(p + k) = make_float2((float)a, (float)b);
+}
+
+// ------------------------------------------------------------------------------------------------
+// tile flags: bit 0 = some ibm > 0, bit 1 = some masked cell, in the flag tile dilated by 2 cells
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_tile_flags(int ny, int nx, long long pitch, const double* __restrict__ ibm, const uint8_t* __restrict__ mask,
+             uint8_t* __restrict__ flags, int ntx) {
+    const int tx = blockIdx.x, ty = blockIdx.y;
+    const int c0 = max(tx * FT_W - 2, 0), c1 = min(tx * FT_W + FT_W + 2, nx);
+    const int r0 = max(ty * FT_H - 2, 0), r1 = min(ty * FT_H + FT_H + 2, ny);
+    const int w = c1 - c0, n = w * (r1 - r0);
+    int f = 0;
+    for (int t = threadIdx.x; t < n; t += 256) {
+        const long long k = (long long)(r0 + t / w) * pitch + c0 + t % w;
+        if (ibm && ibm[k] > 0.0) f |= 1;
+        if (mask && mask[k]) f |= 2;
+    }
+    const int a = __syncthreads_or(f & 1), b = __syncthreads_or(f & 2);
+    if (threadIdx.x == 0) flags[ty * ntx + tx] = (uint8_t)((a ? 1 : 0) | (b ? 2 : 0));
+}
+
+int tile_flags_dims(const Geom& g, int* ntx, int* nty) {
+    *ntx = (g.nx + FT_W - 1) / FT_W;
+    *nty = (g.ny + FT_H - 1) / FT_H;
+    return *ntx * *nty;
+}
+void launch_tile_flags(const Geom& g, const double* ibm, const uint8_t* mask, uint8_t* flags, cudaStream_t s) {
+    int ntx, nty;
+    tile_flags_dims(g, &ntx, &nty);
+    k_tile_flags<<<dim3(ntx, nty), 256, 0, s>>>(g.ny, g.nx, g.pitch, ibm, mask, flags, ntx);
+}
+
+// does any flag tile overlapping columns [c0, c1) x rows [r0, r1) carry one of `bits`?  Block-wide (all threads call).
+__device__ __forceinline__ bool block_tile_flagged(const uint8_t* __restrict__ flags, int ntx, int c0, int c1, int r0, int r1,
+                                                   int bits) {
+    const int tx0 = c0 / FT_W, tx1 = (c1 - 1) / FT_W, ty0 = r0 / FT_H, ty1 = (r1 - 1) / FT_H;
+    const int w = tx1 - tx0 + 1, n = w * (ty1 - ty0 + 1);
+    int f = 0;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) f |= flags[(ty0 + t / w) * ntx + tx0 + t % w] & bits;
+    return __syncthreads_or(f) != 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 fast: u*, v* = u + dt(-C + L) for plain interior cells (no BC, no IBM in the tile)      v5.py:388-407
+// tau = h/(2|V|) min(1, Pe/2) with Pe = |V| h/(nu+1e-10) is evaluated as min(h/(2|V|), h^2/(4(nu+1e-10))) with one
+// rsqrt (algebraically identical to v5.py:155-158; differs in the last ulp only).
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, double half_h, double tau_cap, double dt,
+                                             double uc, double ue, double uw, double un, double us_, double vc, double ve,
+                                             double vw, double vn, double vs_, double& ru, double& rv, double& tau_o) {
+    const double s = uc * uc + vc * vc;
+    double tau = (s > 1e-20) ? fmin(half_h * rsqrt(s), tau_cap) : dt / 2;
+    tau = Rnd<T>::r(tau);
+    tau_o = tau;
+    const double cu = conv_supg_cell<T>(g, uc, vc, uc, ue, uw, un, us_, tau);
+    const double cv = conv_supg_cell<T>(g, uc, vc, vc, ve, vw, vn, vs_, tau);
+    const double lu = lap_cell<T>(g, nu_eff, uc, ue, uw, un, us_);
+    const double lv = lap_cell<T>(g, nu_eff, vc, ve, vw, vn, vs_);
+    ru = axpy_pred<T>(uc, dt, cu, lu);
+    rv = axpy_pred<T>(vc, dt, cv, lv);
+}
+
+template <typename T, bool TAU>
+__global__ void __launch_bounds__(FBT, 5)
+k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
+                 T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const double* __restrict__ ibm,
+                 const double* __restrict__ y, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
+    const int cb = blockIdx.x * FCOLS;
+    const int j0 = cb + 2 * threadIdx.x;
+    const bool flagged = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 1);
+    if (j0 >= g.nx) return;
+    // plain thread: both columns are interior in the local and in the global grid, with both x-neighbours present
+    const bool plain = !flagged && j0 >= 2 && j0 + 3 < g.nx && g.jg0 + j0 >= 2 && g.jg0 + j0 + 3 < g.nxg;
+    const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+    if (!plain) {
+        for (int i = r0; i < r1; ++i) {
+            predictor_point<T>(g, p, ctl, u, v, us, vs, TAU ? tau_out : nullptr, nullptr, ibm, y, i, j0);
+            predictor_point<T>(g, p, ctl, u, v, us, vs, TAU ? tau_out : nullptr, nullptr, ibm, y, i, j0 + 1);
+        }
+        return;
+    }
+    if (r0 == 0) {
+        st2<T>(us, j0, 0.0, 0.0); st2<T>(vs, j0, 0.0, 0.0);
+        if (TAU) st2<T>(tau_out, j0, 0.0, 0.0);
+    }
+    if (r1 == g.ny) {
+        const long long k = (long long)(g.ny - 1) * g.pitch + j0;
+        st2<T>(us, k, 0.0, 0.0); st2<T>(vs, k, 0.0, 0.0);
+        if (TAU) st2<T>(tau_out, k, 0.0, 0.0);
+    }
+    const double dt = ctl->dt;
+    const double half_h = 0.5 * g.hmin, tau_cap = 0.25 * g.hmin * g.hmin / (p.nu_eff + 1e-10);
+    long long k = (long long)lo * g.pitch + j0;
+    D2 um = ld2<T>(u, k - g.pitch), uc = ld2<T>(u, k), vm = ld2<T>(v, k - g.pitch), vc = ld2<T>(v, k);
+    for (int i = lo; i < hi; ++i, k += g.pitch) {
+        const D2 un = ld2<T>(u, k + g.pitch), vn = ld2<T>(v, k + g.pitch);
+        const double uw = ld(u, k - 1), ue = ld(u, k + 2), vw = ld(v, k - 1), ve = ld(v, k + 2);
+        double ru0, rv0, t0, ru1, rv1, t1;
+        predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.x, uc.y, uw, un.x, um.x, vc.x, vc.y, vw, vn.x, vm.x, ru0, rv0, t0);
+        predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.y, ue, uc.x, un.y, um.y, vc.y, ve, vc.x, vn.y, vm.y, ru1, rv1, t1);
+        st2<T>(us, k, ru0, ru1);
+        st2<T>(vs, k, rv0, rv1);
+        if (TAU) st2<T>(tau_out, k, t0, t1);
+        um = uc; uc = un; vm = vc; vc = vn;
+    }
+}
+
+static inline int rows_per_block(const Geom& g, int n_sm) {
+    // enough blocks for ~8 blocks per SM, chunks of 8..64 rows (multiples of the flag tile height)
+    const int bx = (g.nx + FCOLS - 1) / FCOLS;
+    int rpb = 64;
+    while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    return rpb;
+}
+
+bool fast_path_ok(const Geom& g, const void* const* ptrs, int n) {
+    if (g.nx % 2 || g.pitch % 2 || g.nx < 8 || g.ny < 4) return false;
+    for (int k = 0; k < n; ++k)
+        if (ptrs[k] && ((uintptr_t)ptrs[k] & 15)) return false;
+    return true;
+}
+
+void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
+                           void* us, void* vs, void* tau, const double* ibm, const double* y, const uint8_t* flags,
+                           int n_sm, cudaStream_t s) {
+    const int rpb = rows_per_block(g, n_sm);
+    const dim3 grid((g.nx + FCOLS - 1) / FCOLS, (g.ny + rpb - 1) / rpb);
+    const int ntx = (g.nx + FT_W - 1) / FT_W;
+#define PF(T, TAU) k_predictor_fast<T, TAU><<<grid, FBT, 0, s>>>(g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb)
+    if (dtype == 0) { if (tau) PF(double, true); else PF(double, false); }
+    else { if (tau) PF(float, true); else PF(float, false); }
+#undef PF
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 fast: D = div(u*, v*) and the ONE red-black iteration from phi = 0 ("as executed")      v5.py:178-187,202-226
+// Marching thread, 2 columns: keeps D of rows i-1, i, i+1 (computed once each).  An even cell needs phi of its four
+// odd neighbours = D there * dinv / dt_c; three of them are in registers, the fourth (west of .x or east of .y,
+// alternating with the row parity) belongs to the neighbouring thread and is re-derived from 3 extra loads.
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ double div_raw(const Geom& g, double ue, double uw, double vn, double vs_) {
+    return Rnd<T>::r((ue - uw) * g.hdx + (vn - vs_) * g.hdy);
+}
+// phi of an odd cell after the first colour: (a*0 + b*0 + D/dt_c) d, written exactly as the general kernel does
+template <typename T>
+__device__ __forceinline__ double phi_odd(const Geom& g, double D, double inv_dt) {
+    const double rhs = -D * inv_dt;
+    return Rnd<T>::r((g.ax * 0.0 + g.ay * 0.0 - rhs) * g.dinv);
+}
+
+template <typename T, bool DIV>
+__global__ void __launch_bounds__(FBT, 6)
+k_div_rb1_fast(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint8_t* __restrict__ mask,
+               T* __restrict__ phi, T* __restrict__ div_out, double inv_dt, StepCtl* __restrict__ ctl,
+               const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
+    const int cb = blockIdx.x * FCOLS;
+    const int j0 = cb + 2 * threadIdx.x;
+    const bool flagged = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 2);
+    double dabs = 0.0, ch = 0.0;
+    if (j0 < g.nx) {
+        const bool plain = !flagged && j0 >= 2 && j0 + 3 < g.nx && g.jg0 + j0 >= 2 && g.jg0 + j0 + 3 < g.nxg;
+        if (!plain) {
+            for (int i = r0; i < r1; ++i) {
+                divrb1_point<T>(g, us, vs, mask, phi, DIV ? div_out : nullptr, inv_dt, i, j0, dabs, ch);
+                divrb1_point<T>(g, us, vs, mask, phi, DIV ? div_out : nullptr, inv_dt, i, j0 + 1, dabs, ch);
+            }
+        } else {
+            if (r0 == 0) { st2<T>(phi, j0, 0.0, 0.0); if (DIV) st2<T>(div_out, j0, 0.0, 0.0); }
+            if (r1 == g.ny) {
+                const long long kk = (long long)(g.ny - 1) * g.pitch + j0;
+                st2<T>(phi, kk, 0.0, 0.0); if (DIV) st2<T>(div_out, kk, 0.0, 0.0);
+            }
+            const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+            const bool ownx = j0 >= g.own0 && j0 < g.own1, owny = j0 + 1 >= g.own0 && j0 + 1 < g.own1;
+            long long k = (long long)lo * g.pitch + j0;
+            // rows lo-1, lo: D (0 on the border row), and v* rows lo-1 .. lo+1
+            D2 vm = ld2<T>(vs, k - g.pitch), vc = ld2<T>(vs, k), vn = ld2<T>(vs, k + g.pitch);
+            D2 Dm = {0.0, 0.0}, Dc;
+            if (lo - 1 >= 1) {
+                const D2 vmm = ld2<T>(vs, k - 2 * g.pitch), um = ld2<T>(us, k - g.pitch);
+                Dm.x = div_raw<T>(g, um.y, ld(us, k - g.pitch - 1), vc.x, vmm.x);
+                Dm.y = div_raw<T>(g, ld(us, k - g.pitch + 2), um.x, vc.y, vmm.y);
+            }
+            {
+                const D2 uc = ld2<T>(us, k);
+                Dc.x = div_raw<T>(g, uc.y, ld(us, k - 1), vn.x, vm.x);
+                Dc.y = div_raw<T>(g, ld(us, k + 2), uc.x, vn.y, vm.y);
+            }
+            for (int i = lo; i < hi; ++i, k += g.pitch) {
+                // D of row i+1 (0 if that is the border row)
+                D2 Dn = {0.0, 0.0};
+                D2 vnn = {0.0, 0.0};
+                if (i + 1 < g.ny - 1) {
+                    vnn = ld2<T>(vs, k + 2 * g.pitch);
+                    const D2 un = ld2<T>(us, k + g.pitch);
+                    Dn.x = div_raw<T>(g, un.y, ld(us, k + g.pitch - 1), vnn.x, vc.x);
+                    Dn.y = div_raw<T>(g, ld(us, k + g.pitch + 2), un.x, vnn.y, vc.y);
+                }
+                // which of my two cells is even ((i + jg) even)?  .x if (i + jg0 + j0) is even, else .y
+                const bool x_even = ((i + g.jg0 + j0) & 1) == 0;
+                // the foreign odd neighbour: west of .x (column j0-1) or east of .y (column j0+2)
+                const long long kf = x_even ? k - 1 : k + 2;
+                const double uf_e = x_even ? ld(us, k) : ld(us, k + 3);
+                const double uf_w = x_even ? ld(us, k - 2) : ld(us, k + 1);
+                const double Df = div_raw<T>(g, uf_e, uf_w, ld(vs, kf + g.pitch), ld(vs, kf - g.pitch));
+                const double pf = phi_odd<T>(g, Df, inv_dt);
+                double px, py;
+                if (x_even) {
+                    py = phi_odd<T>(g, Dc.y, inv_dt);
+                    const double pn = phi_odd<T>(g, Dn.x, inv_dt), ps = phi_odd<T>(g, Dm.x, inv_dt);
+                    px = (g.ax * (py + pf) + g.ay * (pn + ps) - (-Dc.x * inv_dt)) * g.dinv;
+                } else {
+                    px = phi_odd<T>(g, Dc.x, inv_dt);
+                    const double pn = phi_odd<T>(g, Dn.y, inv_dt), ps = phi_odd<T>(g, Dm.y, inv_dt);
+                    py = (g.ax * (pf + px) + g.ay * (pn + ps) - (-Dc.y * inv_dt)) * g.dinv;
+                }
+                st2<T>(phi, k, px, py);
+                if (DIV) st2<T>(div_out, k, Dc.x, Dc.y);
+                if (ownx) { dabs = fmax(dabs, fabs(Dc.x)); ch = fmax(ch, fabs(px)); }
+                if (owny) { dabs = fmax(dabs, fabs(Dc.y)); ch = fmax(ch, fabs(py)); }
+                Dm = Dc; Dc = Dn; vm = vc; vc = vn; vn = vnn;
+            }
+        }
+    }
+    if (ctl) {
+        block_atomic_max(dabs, &ctl->max_div_pre);
+        block_atomic_max(ch, &ctl->pois_change);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 fast (+ optionally the last clean-divergence correction fused in front of it):
+//   [u,v -= grad(psi)  v5.py:254-256]  ->  max|div| (:421-422) -> BC (:424) -> IBM (:425) -> nanmax|vorticity| (:427-428)
+//   -> nanmean energy (:431-432) -> clip (:437-438) -> post-clip max|u|,|v|.
+// One warp owns a 64-column window (2 columns per lane) and marches down its rows; lanes 0 and 31 are halo lanes (their
+// velocities after the pending correction are only needed as x-neighbours, exchanged with shuffles), lanes 1..30 own 60
+// columns.  Rows i-1, i, i+1 of the corrected velocity and of psi live in registers.  Warps whose tile is flagged
+// (ibm > 0 or masked cells nearby) and the lanes that hold border columns run the general per-cell code.
+// ------------------------------------------------------------------------------------------------
+#define FW_OWN 60                 // columns owned by one warp
+#define FB_OWN (4 * FW_OWN)       // columns owned by one block (4 warps)
+
+template <typename T> __device__ __forceinline__ D2 ld2g(const T* __restrict__ p, long long row_off, int c, bool inb) {
+    return inb ? ld2<T>(p, row_off + c) : D2{0.0, 0.0};
+}
+__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+
+template <typename T, bool PSI>
+__global__ void __launch_bounds__(FBT, 4)
+k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
+                const T* __restrict__ psi, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm,
+                const uint8_t* __restrict__ mask, const double* __restrict__ y, double* __restrict__ ke_part,
+                unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
+    const int own_c0 = blockIdx.x * FB_OWN + warp * FW_OWN;        // first column owned by this warp
+    const int c0 = own_c0 - 2 + 2 * lane;                          // this lane's two columns: c0, c0+1
+    const bool inb = c0 >= 0 && c0 + 1 < g.nx;
+    const bool owner = inb && lane >= 1 && lane <= 30;
+    FinAcc acc;
+    // warp-uniform: is any flag tile over the owned columns set?
+    bool flagged;
+    {
+        const int cA = min(own_c0, g.nx - 1), cB = min(own_c0 + FW_OWN, g.nx);
+        const int tx0 = cA / FT_W, tx1 = max(cB - 1, cA) / FT_W, ty0 = r0 / FT_H, ty1 = (r1 - 1) / FT_H;
+        const int w = tx1 - tx0 + 1, n = w * (ty1 - ty0 + 1);
+        int f = 0;
+        for (int t = lane; t < n; t += 32) f |= flags[(ty0 + t / w) * ntx + tx0 + t % w];
+        flagged = __any_sync(0xffffffffu, f != 0);
+    }
+    if (own_c0 < g.nx) {
+        if (flagged) {
+            if (owner) {
+                for (int i = r0; i < r1; ++i)
+                    for (int c = c0; c < c0 + 2; ++c) {
+                        if (PSI) { const ApplyVel<T> vel{ua, va, psi}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
+                        else { const PlainVel<T> vel{ua, va}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
+                    }
+            }
+        } else {
+            // column predicates
+            const bool inx = inb && c0 >= 1 && g.jg0 + c0 >= 1 && g.jg0 + c0 < g.nxg - 1;                       // c0 interior
+            const bool iny = inb && c0 + 1 < g.nx - 1 && g.jg0 + c0 + 1 >= 1 && g.jg0 + c0 + 1 < g.nxg - 1;    // c0+1 interior
+            const bool plain = owner && c0 >= 2 && c0 + 3 < g.nx && g.jg0 + c0 >= 2 && g.jg0 + c0 + 3 < g.nxg;
+            const bool ownx = c0 >= g.own0 && c0 < g.own1, owny = c0 + 1 >= g.own0 && c0 + 1 < g.own1;
+            const double i2dx = 1.0 / Rnd<T>::r(g.two_dx), i2dy = 1.0 / Rnd<T>::r(g.two_dy);
+            const double vmax = p.max_velocity;
+            const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+            // general per-cell code for the wall rows and for owned cells of non-plain lanes
+            auto general_cell = [&](int i, int c) {
+                if (PSI) { const ApplyVel<T> vel{ua, va, psi}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
+                else { const PlainVel<T> vel{ua, va}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
+            };
+            if (owner && r0 == 0) { general_cell(0, c0); general_cell(0, c0 + 1); }
+            if (owner && r1 == g.ny) { general_cell(g.ny - 1, c0); general_cell(g.ny - 1, c0 + 1); }
+            // corrected velocity of one row from its raw values and three psi rows (all lanes, convergent: shuffles)
+            auto apply_row = [&](int row, const D2& ur, const D2& vr, const D2& pS, const D2& pC, const D2& pN, D2& fu, D2& fv) {
+                fu = ur; fv = vr;
+                if (PSI) {
+                    const double pW = shfl_up1(pC.y), pE = shfl_dn1(pC.x);
+                    if (row >= 1 && row < g.ny - 1) {
+                        if (inx) {
+                            fu.x = Rnd<T>::r(ur.x - Rnd<T>::r((pC.y - pW) * g.hdx));
+                            fv.x = Rnd<T>::r(vr.x - Rnd<T>::r((pN.x - pS.x) * g.hdy));
+                        }
+                        if (iny) {
+                            fu.y = Rnd<T>::r(ur.y - Rnd<T>::r((pE - pC.x) * g.hdx));
+                            fv.y = Rnd<T>::r(vr.y - Rnd<T>::r((pN.y - pS.y) * g.hdy));
+                        }
+                    }
+                }
+            };
+            long long ro = (long long)lo * g.pitch;
+            D2 pm = {0, 0}, pc = {0, 0}, pn = {0, 0};     // psi rows (i), (i+1), (i+2) while row i is processed
+            D2 fum, fvm, fuc, fvc;
+            {   // rows lo-1 and lo
+                D2 pmm = {0, 0};
+                if (PSI) {
+                    if (lo - 2 >= 0) pmm = ld2g<T>(psi, ro - 2 * g.pitch, c0, inb);
+                    pm = ld2g<T>(psi, ro - g.pitch, c0, inb);
+                    pc = ld2g<T>(psi, ro, c0, inb);
+                    pn = ld2g<T>(psi, ro + g.pitch, c0, inb);
+                }
+                apply_row(lo - 1, ld2g<T>(ua, ro - g.pitch, c0, inb), ld2g<T>(va, ro - g.pitch, c0, inb), pmm, pm, pc, fum, fvm);
+                apply_row(lo, ld2g<T>(ua, ro, c0, inb), ld2g<T>(va, ro, c0, inb), pm, pc, pn, fuc, fvc);
+                pm = pc; pc = pn;      // now pm = psi(lo), pc = psi(lo+1)
+            }
+            for (int i = lo; i < hi; ++i, ro += g.pitch) {
+                // row i+1: raw velocity, psi row i+2 (exists unless i+1 is the border row, where no correction applies)
+                if (PSI) pn = (i + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
+                D2 fun, fvn;
+                apply_row(i + 1, ld2g<T>(ua, ro + g.pitch, c0, inb), ld2g<T>(va, ro + g.pitch, c0, inb), pm, pc, pn, fun, fvn);
+                const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), fvW = shfl_up1(fvc.y), fvE = shfl_dn1(fvc.x);
+                if (plain) {
+                    const double dx_ = Rnd<T>::r((fuc.y - fuW) * g.hdx + (fvn.x - fvm.x) * g.hdy);
+                    const double dy_ = Rnd<T>::r((fuE - fuc.x) * g.hdx + (fvn.y - fvm.y) * g.hdy);
+                    const double wx = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvc.y - fvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.x - fum.x) * i2dy));
+                    const double wy = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvE - fvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.y - fum.y) * i2dy));
+                    const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.x * fuc.x) + Rnd<T>::r(fvc.x * fvc.x)));
+                    const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.y * fuc.y) + Rnd<T>::r(fvc.y * fvc.y)));
+                    const double cux = fmin(fmax(fuc.x, -vmax), vmax), cuy = fmin(fmax(fuc.y, -vmax), vmax);
+                    const double cvx = fmin(fmax(fvc.x, -vmax), vmax), cvy = fmin(fmax(fvc.y, -vmax), vmax);
+                    // np.clip propagates NaN; fmin/fmax would drop it
+                    st2<T>(u, ro + c0, fuc.x == fuc.x ? cux : fuc.x, fuc.y == fuc.y ? cuy : fuc.y);
+                    st2<T>(v, ro + c0, fvc.x == fvc.x ? cvx : fvc.x, fvc.y == fvc.y ? cvy : fvc.y);
+                    if (ownx) {
+                        acc.dmax = fmax(acc.dmax, fabs(dx_)); acc.wmax = fmax(acc.wmax, fabs(wx));
+                        if (ex == ex) { acc.e += ex; acc.cnt += 1; }
+                        if (!isfinite(ex)) acc.bad = 1;
+                        acc.mu = fmax(acc.mu, fabs(cux)); acc.mv = fmax(acc.mv, fabs(cvx));
+                    }
+                    if (owny) {
+                        acc.dmax = fmax(acc.dmax, fabs(dy_)); acc.wmax = fmax(acc.wmax, fabs(wy));
+                        if (ey == ey) { acc.e += ey; acc.cnt += 1; }
+                        if (!isfinite(ey)) acc.bad = 1;
+                        acc.mu = fmax(acc.mu, fabs(cuy)); acc.mv = fmax(acc.mv, fabs(cvy));
+                    }
+                } else if (owner) {
+                    general_cell(i, c0); general_cell(i, c0 + 1);
+                }
+                fum = fuc; fvm = fvc; fuc = fun; fvc = fvn;
+                pm = pc; pc = pn;
+            }
+        }
+    }
+    finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * gridDim.x + blockIdx.x);
+}
+
+void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
+                         void* div_out, double inv_dt, StepCtl* ctl, const uint8_t* flags, int n_sm, cudaStream_t s) {
+    const int rpb = rows_per_block(g, n_sm);
+    const dim3 grid((g.nx + FCOLS - 1) / FCOLS, (g.ny + rpb - 1) / rpb);
+    const int ntx = (g.nx + FT_W - 1) / FT_W;
+#define DF(T, DIV) k_div_rb1_fast<T, DIV><<<grid, FBT, 0, s>>>(g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, inv_dt, ctl, flags, ntx, rpb)
+    if (dtype == 0) { if (div_out) DF(double, true); else DF(double, false); }
+    else { if (div_out) DF(float, true); else DF(float, false); }
+#undef DF
+}
+
+static inline dim3 finalize_fast_grid(const Geom& g, int n_sm, int* rpb_out) {
+    const int bx = (g.nx + FB_OWN - 1) / FB_OWN;
+    int rpb = 64;
+    while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    *rpb_out = rpb;
+    return dim3(bx, (g.ny + rpb - 1) / rpb);
+}
+int finalize_fast_num_partials(const Geom& g, int n_sm) {
+    int rpb;
+    const dim3 gr = finalize_fast_grid(g, n_sm, &rpb);
+    return (int)(gr.x * gr.y);
+}
+// psi != NULL: the pending correction u,v -= grad(psi) of the last clean-divergence iteration is applied on the fly
+void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
+                          const void* psi, void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
+                          double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags, int n_sm,
+                          cudaStream_t s) {
+    int rpb;
+    const dim3 grid = finalize_fast_grid(g, n_sm, &rpb);
+    const int ntx = (g.nx + FT_W - 1) / FT_W;
+#define FF(T, PSI) k_finalize_fast<T, PSI><<<grid, FBT, 0, s>>>(g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
+    if (dtype == 0) { if (psi) FF(double, true); else FF(double, false); }
+    else { if (psi) FF(float, true); else FF(float, false); }
+#undef FF
+}
+
+}  // namespace b200cfd

@@ -3,6 +3,7 @@
 // All arithmetic is done in double after the load; values the reference materialises as arrays of the
 // field dtype are rounded to T at the same points (Rnd<T>), so fp32 storage follows the reference too.
 #include "kernels.h"
+#include "cellmath.cuh"
 
 namespace b200cfd {
 
@@ -10,52 +11,6 @@ namespace b200cfd {
 #define BY 4
 static inline dim3 grid2d(const Geom& g) { return dim3((g.nx + BX - 1) / BX, (g.ny + BY - 1) / BY); }
 static const dim3 kBlock(BX, BY);
-
-template <typename T> __device__ __forceinline__ double ld(const T* p, long long k) { return (double)p[k]; }
-
-// interior in the GLOBAL grid and with all four neighbours present locally
-__device__ __forceinline__ bool is_interior(const Geom& g, int i, int j) {
-    const int jg = g.jg0 + j;
-    return i >= 1 && i < g.ny - 1 && j >= 1 && j < g.nx - 1 && jg >= 1 && jg < g.nxg - 1;
-}
-
-// ------------------------------------------------------------------------------------------------
-// shared per-cell math
-// ------------------------------------------------------------------------------------------------
-// v5.py:149-162
-template <typename T>
-__device__ __forceinline__ double tau_cell(const Geom& g, double uc, double vc, double dt, double nu_eff) {
-    const double vel = sqrt(uc * uc + vc * vc);
-    double t;
-    if (vel > 1e-10) {
-        const double Pe = vel * g.hmin / (nu_eff + 1e-10);
-        t = g.hmin / (2 * vel) * fmin(1.0, Pe / 2.0);
-    } else {
-        t = dt / 2;
-    }
-    return Rnd<T>::r(t);
-}
-// v5.py:127-147
-template <typename T>
-__device__ __forceinline__ double conv_supg_cell(const Geom& g, double uc, double vc, double pc, double pe, double pw,
-                                                 double pn, double ps, double tau) {
-    double c = uc * ((pe - pw) * g.qdx) + vc * ((pn - ps) * g.qdy);
-    if (tau > 0) c -= tau * (uc * ((pe - 2 * pc + pw) * g.hdx2) + vc * ((pn - 2 * pc + ps) * g.hdy2));
-    return Rnd<T>::r(c);
-}
-// v5.py:112-125
-template <typename T>
-__device__ __forceinline__ double conv_upwind_cell(const Geom& g, double uc, double vc, double pc, double pe, double pw,
-                                                   double pn, double ps) {
-    const double dpx = uc > 0 ? (pc - pw) * g.rdx : (pe - pc) * g.rdx;
-    const double dpy = vc > 0 ? (pc - ps) * g.rdy : (pn - pc) * g.rdy;
-    return Rnd<T>::r(uc * dpx + vc * dpy);
-}
-// v5.py:164-176
-template <typename T>
-__device__ __forceinline__ double lap_cell(const Geom& g, double nu_eff, double pc, double pe, double pw, double pn, double ps) {
-    return Rnd<T>::r(nu_eff * ((pe - 2 * pc + pw) * g.ax + (pn - 2 * pc + ps) * g.ay));
-}
 
 // ------------------------------------------------------------------------------------------------
 // unit kernels
@@ -148,11 +103,6 @@ __global__ void k_smagorinsky(Geom g, const T* __restrict__ u, const T* __restri
     nu_t[k] = (T)out;
 }
 
-// inflow profile value, v5.py:351-353
-__device__ __forceinline__ double inflow_u(double V_inf, double y_max, double yi, double pert_scale, double phase) {
-    return V_inf * (1 + pert_scale * sin(2 * M_PI * yi / y_max + phase));
-}
-
 // v5.py:349-360: one thread per border cell; order inflow, outflow, walls (corners end as 0)
 template <typename T>
 __global__ void k_apply_bc(Geom g, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ y, double V_inf,
@@ -199,66 +149,13 @@ __global__ void k_apply_ibm(Geom g, T* __restrict__ u, T* __restrict__ v, const 
 // columns: they are not written here (the halo exchange fills them).
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __forceinline__ void predict_cell(const Geom& g, const Phys& p, const T* __restrict__ u,
-                                             const T* __restrict__ v, const T* __restrict__ nu_t, long long k,
-                                             double dt, double& ru, double& rv, double& tau_o) {
-    const double uc = ld(u, k), vc = ld(v, k);
-    const double ue = ld(u, k + 1), uw = ld(u, k - 1), un = ld(u, k + g.pitch), us = ld(u, k - g.pitch);
-    const double ve = ld(v, k + 1), vw = ld(v, k - 1), vn = ld(v, k + g.pitch), vs = ld(v, k - g.pitch);
-    const double ne = nu_t ? Rnd<T>::r(p.nu_eff + ld(nu_t, k)) : p.nu_eff;
-    double cu, cv;
-    if (p.use_supg) {
-        const double tau = tau_cell<T>(g, uc, vc, dt, ne);
-        tau_o = tau;
-        cu = conv_supg_cell<T>(g, uc, vc, uc, ue, uw, un, us, tau);
-        cv = conv_supg_cell<T>(g, uc, vc, vc, ve, vw, vn, vs, tau);
-    } else {
-        tau_o = 0.0;
-        cu = conv_upwind_cell<T>(g, uc, vc, uc, ue, uw, un, us);
-        cv = conv_upwind_cell<T>(g, uc, vc, vc, ve, vw, vn, vs);
-    }
-    const double lu = lap_cell<T>(g, ne, uc, ue, uw, un, us);
-    const double lv = lap_cell<T>(g, ne, vc, ve, vw, vn, vs);
-    ru = axpy_pred<T>(uc, dt, cu, lu);
-    rv = axpy_pred<T>(vc, dt, cv, lv);
-}
-
-template <typename T>
 __global__ void __launch_bounds__(BX* BY)
 k_predictor(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
             T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const T* __restrict__ nu_t,
             const double* __restrict__ ibm, const double* __restrict__ y) {
     const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
     if (i >= g.ny || j >= g.nx) return;
-    const int jg = g.jg0 + j;
-    const long long k = i * g.pitch + j;
-    const bool wall = (i == 0 || i == g.ny - 1);
-    const bool inflow = (jg == 0), outflow = (jg == g.nxg - 1);
-    const bool ledge = !inflow && !outflow && (j == 0 || j == g.nx - 1);   // outermost halo column of a slab: no stencil
-    const double dt = ctl->dt, fs = ctl->fs;
-    double ru, rv, tau_o = 0.0;
-    if (wall) {
-        ru = 0.0; rv = 0.0;
-    } else if (ledge) {
-        ru = ld(u, k); rv = ld(v, k);
-    } else if (inflow) {
-        ru = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase));
-        rv = 0.0;
-    } else if (outflow) {
-        double t;
-        if (jg - 1 == 0) { ru = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); rv = 0.0; }
-        else predict_cell<T>(g, p, u, v, nu_t, k - 1, dt, ru, rv, t);
-    } else {
-        predict_cell<T>(g, p, u, v, nu_t, k, dt, ru, rv, tau_o);
-    }
-    const double m = ibm[k];
-    if (m > 0) {
-        ru = Rnd<T>::r(ru * (1.0 - m * fs));
-        rv = Rnd<T>::r(rv * (1.0 - m * fs));
-    }
-    us[k] = (T)ru;
-    vs[k] = (T)rv;
-    if (tau_out) tau_out[k] = (T)tau_o;
+    predictor_point<T>(g, p, ctl, u, v, us, vs, tau_out, nu_t, ibm, y, i, j);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -292,74 +189,15 @@ k_correct(Geom g, StepCtl* __restrict__ ctl, const T* __restrict__ us, const T* 
 // BC+IBM are pointwise in (ua, va), so the vorticity stencil re-evaluates them at the 4 neighbours.
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __forceinline__ void bcibm_cell(const Geom& g, const Phys& p, const StepCtl* ctl, const T* __restrict__ ua,
-                                           const T* __restrict__ va, const double* __restrict__ ibm,
-                                           const double* __restrict__ y, int i, int j, double& fu, double& fv) {
-    const int jg = g.jg0 + j;
-    const long long k = i * g.pitch + j;
-    if (i == 0 || i == g.ny - 1) { fu = 0.0; fv = 0.0; }
-    else if (jg == 0) { fu = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); fv = 0.0; }
-    else if (jg == g.nxg - 1) {
-        if (jg - 1 == 0) { fu = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], ctl->pert_scale, ctl->phase)); fv = 0.0; }
-        else { fu = ld(ua, k - 1); fv = ld(va, k - 1); }
-    } else { fu = ld(ua, k); fv = ld(va, k); }
-    const double m = ibm[k];
-    if (m > 0) {
-        fu = Rnd<T>::r(fu * (1.0 - m * ctl->fs));
-        fv = Rnd<T>::r(fv * (1.0 - m * ctl->fs));
-    }
-}
-
-template <typename T>
 __global__ void __launch_bounds__(BX* BY)
 k_finalize(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
            T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm, const uint8_t* __restrict__ mask,
            const double* __restrict__ y, double* __restrict__ ke_part, unsigned long long* __restrict__ cnt_part) {
     const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
-    double dmax = 0.0, wmax = 0.0, e = 0.0, mu = 0.0, mv = 0.0;
-    unsigned cnt = 0, bad = 0;
-    // every local cell is computed (halo columns redundantly); only OWNED columns enter the reductions
-    const bool own = i < g.ny && j >= g.own0 && j < g.own1;
-    if (i < g.ny && j < g.nx) {
-        const long long k = i * g.pitch + j;
-        double fu, fv;
-        bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j, fu, fv);
-        if (is_interior(g, i, j)) {
-            if (own) dmax = fabs(Rnd<T>::r((ld(ua, k + 1) - ld(ua, k - 1)) * g.hdx + (ld(va, k + g.pitch) - ld(va, k - g.pitch)) * g.hdy));
-            if (own && !(mask && mask[k])) {
-                double eu, ev, wu, wv, nu_, nv, su, sv;
-                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j + 1, eu, ev);
-                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i, j - 1, wu, wv);
-                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i + 1, j, nu_, nv);
-                bcibm_cell<T>(g, p, ctl, ua, va, ibm, y, i - 1, j, su, sv);
-                const double w = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(ev - wv) / Rnd<T>::r(g.two_dx)) -
-                                           Rnd<T>::r(Rnd<T>::r(nu_ - su) / Rnd<T>::r(g.two_dy)));
-                wmax = fabs(w);   // NaN is dropped by fmax in the reduction (nanmax)
-            }
-        }
-        const double en = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fu * fu) + Rnd<T>::r(fv * fv)));
-        if (own && en == en) { e = en; cnt = 1; }
-        if (own && (!isfinite(fu) || !isfinite(fv))) bad = 1;
-        const double cu = fmin(fmax(fu, -p.max_velocity), p.max_velocity);
-        const double cv = fmin(fmax(fv, -p.max_velocity), p.max_velocity);
-        // np.clip propagates NaN; fmin/fmax would drop it
-        u[k] = (T)(fu == fu ? cu : fu);
-        v[k] = (T)(fv == fv ? cv : fv);
-        if (own) { mu = fabs(cu); mv = fabs(cv); }
-    }
-    block_atomic_max(dmax, &ctl->max_div_post);
-    block_atomic_max(wmax, &ctl->max_vort);
-    block_atomic_max(mu, &ctl->max_u);
-    block_atomic_max(mv, &ctl->max_v);
-    const double bs = block_sum(e);
-    const double bc = block_sum((double)cnt);
-    const int nbad = __syncthreads_or((int)bad);
-    if (threadIdx.x == 0 && threadIdx.y == 0) {
-        const int b = blockIdx.y * gridDim.x + blockIdx.x;
-        ke_part[b] = bs;
-        cnt_part[b] = (unsigned long long)(bc + 0.5);
-        if (nbad) atomicOr(&ctl->nonfinite, 1u);
-    }
+    FinAcc acc;
+    const PlainVel<T> vel{ua, va};
+    if (i < g.ny && j < g.nx) finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, j, acc);
+    finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * gridDim.x + blockIdx.x);
 }
 
 // max|u|, max|v| of the bound state (set_step / first step: what adaptive_time_step reads, v5.py:322)

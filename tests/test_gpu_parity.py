@@ -249,3 +249,45 @@ def test_time_step_host_round_trip_matches_resident():
     assert np.array_equal(uh, a.u) and np.array_equal(vh, a.v)
     assert last.step == 5
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_general_kernels_path_vs_oracle(monkeypatch, f32):
+    """B200CFD_NO_FAST=1 selects the general one-thread-per-cell kernels (the path for odd nx / LES / upwind); it must
+    meet the same tolerances as the row-marching fast kernels that the other tests exercise."""
+    monkeypatch.setenv("B200CFD_NO_FAST", "1")
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=640, ny=200, memory_efficient=f32)
+    so, sg = OracleTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg)
+    so.step = sg.step = 990
+    for _ in range(20):
+        so.time_step()
+    sg.advance(20)
+    tol = TOL["f32" if f32 else "f64"]
+    assert rel_l2(sg.u, so.u) <= tol and rel_l2(sg.v, so.v) <= tol * (1 if not f32 else 3)
+    assert rel_l2(sg.phi, so.phi) <= tol * (1 if not f32 else 10)
+    sg.close()
+
+
+@pytest.mark.parametrize("nx,ny", [(641, 77), (250, 33), (1026, 130)])
+def test_odd_and_ragged_grids_vs_oracle(nx, ny):
+    """odd nx takes the general kernels, even nx that is not a multiple of the tile widths takes the fast ones."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=nx, ny=ny, memory_efficient=False)
+    so, sg = OracleTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg)
+    so.step = sg.step = 995
+    for _ in range(12):
+        so.time_step()
+    sg.advance(12)
+    for name in ("u", "v", "phi", "u_star", "v_star", "div_u_star", "tau_supg"):
+        assert rel_l2(getattr(sg, name), getattr(so, name)) <= 1e-12, name
+    sg._sync_scalars()
+    for k in range(1, 13):
+        a, b = sg.scalars[-k], so.scalars[-k]
+        for key, idx in (("max_div_pre", 1), ("max_grad_phi", 2), ("max_div_post", 3), ("max_vorticity", 4), ("mean_energy", 5)):
+            assert abs(a[key] - b[idx]) <= 1e-9 * max(abs(b[idx]), 1e-30), (key, k)
+    sg.close()

@@ -20,6 +20,10 @@ namespace b200cfd {
 #define FBT 128      // threads per block of the marching kernels
 #define FCOLS 256    // columns per block (2 per thread)
 
+#define FPF 6        // L2 prefetch distance of the marching kernels, rows
+
+__device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 struct D2 { double x, y; };
 template <typename T> __device__ __forceinline__ D2 ld2(const T* __restrict__ p, long long k);
 template <> __device__ __forceinline__ D2 ld2<double>(const double* __restrict__ p, long long k) {
@@ -100,6 +104,16 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
     rv = axpy_pred<T>(vc, dt, cv, lv);
 }
 
+// column classes of one lane's two columns
+enum { COL_INTERIOR = 0, COL_INFLOW = 1, COL_OUTFLOW = 2, COL_COPY = 3 };
+__device__ __forceinline__ int col_class(const Geom& g, int c) {
+    const int cg = g.jg0 + c;
+    if (cg == 0) return COL_INFLOW;
+    if (cg == g.nxg - 1) return COL_OUTFLOW;
+    if (c == 0 || c == g.nx - 1) return COL_COPY;        // outermost halo column of a slab: no stencil
+    return COL_INTERIOR;
+}
+
 template <typename T, bool TAU>
 __global__ void __launch_bounds__(FBT, 5)
 k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
@@ -108,18 +122,11 @@ k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __res
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int cb = blockIdx.x * FCOLS;
     const int j0 = cb + 2 * threadIdx.x;
-    const bool flagged = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 1);
+    const bool has_ibm = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 1);
     if (j0 >= g.nx) return;
-    // plain thread: both columns are interior in the local and in the global grid, with both x-neighbours present
-    const bool plain = !flagged && j0 >= 2 && j0 + 3 < g.nx && g.jg0 + j0 >= 2 && g.jg0 + j0 + 3 < g.nxg;
+    const int cx = col_class(g, j0), cy = col_class(g, j0 + 1);
+    const bool hw = j0 >= 1, he = j0 + 2 < g.nx;             // west / east neighbour columns exist
     const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
-    if (!plain) {
-        for (int i = r0; i < r1; ++i) {
-            predictor_point<T>(g, p, ctl, u, v, us, vs, TAU ? tau_out : nullptr, nullptr, ibm, y, i, j0);
-            predictor_point<T>(g, p, ctl, u, v, us, vs, TAU ? tau_out : nullptr, nullptr, ibm, y, i, j0 + 1);
-        }
-        return;
-    }
     if (r0 == 0) {
         st2<T>(us, j0, 0.0, 0.0); st2<T>(vs, j0, 0.0, 0.0);
         if (TAU) st2<T>(tau_out, j0, 0.0, 0.0);
@@ -129,20 +136,42 @@ k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __res
         st2<T>(us, k, 0.0, 0.0); st2<T>(vs, k, 0.0, 0.0);
         if (TAU) st2<T>(tau_out, k, 0.0, 0.0);
     }
-    const double dt = ctl->dt;
+    if (lo >= hi) return;
+    const double dt = ctl->dt, fs = ctl->fs, pert = ctl->pert_scale, phase = ctl->phase;
     const double half_h = 0.5 * g.hmin, tau_cap = 0.25 * g.hmin * g.hmin / (p.nu_eff + 1e-10);
     long long k = (long long)lo * g.pitch + j0;
     D2 um = ld2<T>(u, k - g.pitch), uc = ld2<T>(u, k), vm = ld2<T>(v, k - g.pitch), vc = ld2<T>(v, k);
+    D2 un = ld2<T>(u, k + g.pitch), vn = ld2<T>(v, k + g.pitch);
+    double uw = hw ? ld(u, k - 1) : 0.0, ue = he ? ld(u, k + 2) : 0.0, vw = hw ? ld(v, k - 1) : 0.0, ve = he ? ld(v, k + 2) : 0.0;
     for (int i = lo; i < hi; ++i, k += g.pitch) {
-        const D2 un = ld2<T>(u, k + g.pitch), vn = ld2<T>(v, k + g.pitch);
-        const double uw = ld(u, k - 1), ue = ld(u, k + 2), vw = ld(v, k - 1), ve = ld(v, k + 2);
-        double ru0, rv0, t0, ru1, rv1, t1;
-        predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.x, uc.y, uw, un.x, um.x, vc.x, vc.y, vw, vn.x, vm.x, ru0, rv0, t0);
-        predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.y, ue, uc.x, un.y, um.y, vc.y, ve, vc.x, vn.y, vm.y, ru1, rv1, t1);
+        // software pipeline: the loads of the NEXT iteration (row i+2, and the x-neighbours of row i+1) are issued now
+        D2 un2 = {0, 0}, vn2 = {0, 0};
+        double uw1 = 0.0, ue1 = 0.0, vw1 = 0.0, ve1 = 0.0;
+        if (i + 1 < hi) {
+            un2 = ld2<T>(u, k + 2 * g.pitch); vn2 = ld2<T>(v, k + 2 * g.pitch);
+            if (hw) { uw1 = ld(u, k + g.pitch - 1); vw1 = ld(v, k + g.pitch - 1); }
+            if (he) { ue1 = ld(u, k + g.pitch + 2); ve1 = ld(v, k + g.pitch + 2); }
+        }
+        if (i + FPF < g.ny) { pf_l2(u + k + FPF * g.pitch); pf_l2(v + k + FPF * g.pitch); }
+        double ru0, rv0, t0 = 0.0, ru1, rv1, t1 = 0.0;
+        if (cx == COL_INTERIOR)
+            predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.x, uc.y, uw, un.x, um.x, vc.x, vc.y, vw, vn.x, vm.x, ru0, rv0, t0);
+        else if (cx == COL_INFLOW) { ru0 = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], pert, phase)); rv0 = 0.0; }
+        else { ru0 = uc.x; rv0 = vc.x; }
+        if (cy == COL_INTERIOR)
+            predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.y, ue, uc.x, un.y, um.y, vc.y, ve, vc.x, vn.y, vm.y, ru1, rv1, t1);
+        else if (cy == COL_OUTFLOW) { ru1 = ru0; rv1 = rv0; }        // BC copies the already predicted column nx-2 (v5.py:355-356)
+        else { ru1 = uc.y; rv1 = vc.y; }
+        if (has_ibm) {
+            const double2 m = *reinterpret_cast<const double2*>(ibm + k);
+            if (m.x > 0) { ru0 = Rnd<T>::r(ru0 * (1.0 - m.x * fs)); rv0 = Rnd<T>::r(rv0 * (1.0 - m.x * fs)); }
+            if (m.y > 0) { ru1 = Rnd<T>::r(ru1 * (1.0 - m.y * fs)); rv1 = Rnd<T>::r(rv1 * (1.0 - m.y * fs)); }
+        }
         st2<T>(us, k, ru0, ru1);
         st2<T>(vs, k, rv0, rv1);
         if (TAU) st2<T>(tau_out, k, t0, t1);
-        um = uc; uc = un; vm = vc; vc = vn;
+        um = uc; uc = un; vm = vc; vc = vn; un = un2; vn = vn2;
+        uw = uw1; ue = ue1; vw = vw1; ve = ve1;
     }
 }
 
@@ -198,71 +227,76 @@ k_div_rb1_fast(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int cb = blockIdx.x * FCOLS;
     const int j0 = cb + 2 * threadIdx.x;
-    const bool flagged = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 2);
+    const bool has_mask = mask && block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 2);
     double dabs = 0.0, ch = 0.0;
+    const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
     if (j0 < g.nx) {
-        const bool plain = !flagged && j0 >= 2 && j0 + 3 < g.nx && g.jg0 + j0 >= 2 && g.jg0 + j0 + 3 < g.nxg;
-        if (!plain) {
-            for (int i = r0; i < r1; ++i) {
-                divrb1_point<T>(g, us, vs, mask, phi, DIV ? div_out : nullptr, inv_dt, i, j0, dabs, ch);
-                divrb1_point<T>(g, us, vs, mask, phi, DIV ? div_out : nullptr, inv_dt, i, j0 + 1, dabs, ch);
+        if (r0 == 0) { st2<T>(phi, j0, 0.0, 0.0); if (DIV) st2<T>(div_out, j0, 0.0, 0.0); }
+        if (r1 == g.ny) {
+            const long long kk = (long long)(g.ny - 1) * g.pitch + j0;
+            st2<T>(phi, kk, 0.0, 0.0); if (DIV) st2<T>(div_out, kk, 0.0, 0.0);
+        }
+    }
+    if (j0 < g.nx && lo < hi) {
+        // interior columns (local and global); border columns keep D = 0, phi = 0
+        const bool xin = col_class(g, j0) == COL_INTERIOR, yin = col_class(g, j0 + 1) == COL_INTERIOR;
+        // the foreign odd neighbour exists and is interior: west of .x is column j0-1, east of .y is column j0+2
+        const bool fw = xin && j0 - 1 >= 1 && g.jg0 + j0 - 1 >= 1;
+        const bool fe = yin && j0 + 2 < g.nx - 1 && g.jg0 + j0 + 2 < g.nxg - 1;
+        const bool ownx = j0 >= g.own0 && j0 < g.own1, owny = j0 + 1 >= g.own0 && j0 + 1 < g.own1;
+        long long k = (long long)lo * g.pitch + j0;
+        // D of one row of my two columns from u* of that row (pair + the two x-neighbours) and v* above / below
+        auto div_row = [&](long long kr, const D2& vN, const D2& vS) {
+            const D2 uc = ld2<T>(us, kr);
+            D2 d = {0.0, 0.0};
+            if (xin) d.x = div_raw<T>(g, uc.y, ld(us, kr - 1), vN.x, vS.x);
+            if (yin) d.y = div_raw<T>(g, ld(us, kr + 2), uc.x, vN.y, vS.y);
+            return d;
+        };
+        D2 vm = ld2<T>(vs, k - g.pitch), vc = ld2<T>(vs, k), vn = ld2<T>(vs, k + g.pitch);
+        D2 Dm = {0.0, 0.0};
+        if (lo - 1 >= 1) Dm = div_row(k - g.pitch, vc, ld2<T>(vs, k - 2 * g.pitch));
+        D2 Dc = div_row(k, vn, vm);
+        uchar2 mm = make_uchar2(0, 0), mc = mm, mn = mm;
+        if (has_mask) {
+            mm = *reinterpret_cast<const uchar2*>(mask + k - g.pitch);
+            mc = *reinterpret_cast<const uchar2*>(mask + k);
+        }
+        for (int i = lo; i < hi; ++i, k += g.pitch) {
+            if (i + FPF < g.ny) { pf_l2(us + k + FPF * g.pitch); pf_l2(vs + k + FPF * g.pitch); }
+            D2 Dn = {0.0, 0.0}, vnn = {0.0, 0.0};
+            if (i + 1 < g.ny - 1) {                        // D of row i+1 (0 if that is the border row)
+                vnn = ld2<T>(vs, k + 2 * g.pitch);
+                Dn = div_row(k + g.pitch, vnn, vc);
             }
-        } else {
-            if (r0 == 0) { st2<T>(phi, j0, 0.0, 0.0); if (DIV) st2<T>(div_out, j0, 0.0, 0.0); }
-            if (r1 == g.ny) {
-                const long long kk = (long long)(g.ny - 1) * g.pitch + j0;
-                st2<T>(phi, kk, 0.0, 0.0); if (DIV) st2<T>(div_out, kk, 0.0, 0.0);
-            }
-            const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
-            const bool ownx = j0 >= g.own0 && j0 < g.own1, owny = j0 + 1 >= g.own0 && j0 + 1 < g.own1;
-            long long k = (long long)lo * g.pitch + j0;
-            // rows lo-1, lo: D (0 on the border row), and v* rows lo-1 .. lo+1
-            D2 vm = ld2<T>(vs, k - g.pitch), vc = ld2<T>(vs, k), vn = ld2<T>(vs, k + g.pitch);
-            D2 Dm = {0.0, 0.0}, Dc;
-            if (lo - 1 >= 1) {
-                const D2 vmm = ld2<T>(vs, k - 2 * g.pitch), um = ld2<T>(us, k - g.pitch);
-                Dm.x = div_raw<T>(g, um.y, ld(us, k - g.pitch - 1), vc.x, vmm.x);
-                Dm.y = div_raw<T>(g, ld(us, k - g.pitch + 2), um.x, vc.y, vmm.y);
-            }
-            {
-                const D2 uc = ld2<T>(us, k);
-                Dc.x = div_raw<T>(g, uc.y, ld(us, k - 1), vn.x, vm.x);
-                Dc.y = div_raw<T>(g, ld(us, k + 2), uc.x, vn.y, vm.y);
-            }
-            for (int i = lo; i < hi; ++i, k += g.pitch) {
-                // D of row i+1 (0 if that is the border row)
-                D2 Dn = {0.0, 0.0};
-                D2 vnn = {0.0, 0.0};
-                if (i + 1 < g.ny - 1) {
-                    vnn = ld2<T>(vs, k + 2 * g.pitch);
-                    const D2 un = ld2<T>(us, k + g.pitch);
-                    Dn.x = div_raw<T>(g, un.y, ld(us, k + g.pitch - 1), vnn.x, vc.x);
-                    Dn.y = div_raw<T>(g, ld(us, k + g.pitch + 2), un.x, vnn.y, vc.y);
-                }
-                // which of my two cells is even ((i + jg) even)?  .x if (i + jg0 + j0) is even, else .y
-                const bool x_even = ((i + g.jg0 + j0) & 1) == 0;
-                // the foreign odd neighbour: west of .x (column j0-1) or east of .y (column j0+2)
+            if (has_mask) mn = *reinterpret_cast<const uchar2*>(mask + k + g.pitch);
+            // which of my two cells is even ((i + jg) even)?  .x if (i + jg0 + j0) is even, else .y
+            const bool x_even = ((i + g.jg0 + j0) & 1) == 0;
+            double pf = 0.0;                               // phi of the foreign odd neighbour (0: border or masked)
+            if (x_even ? fw : fe) {
                 const long long kf = x_even ? k - 1 : k + 2;
-                const double uf_e = x_even ? ld(us, k) : ld(us, k + 3);
-                const double uf_w = x_even ? ld(us, k - 2) : ld(us, k + 1);
-                const double Df = div_raw<T>(g, uf_e, uf_w, ld(vs, kf + g.pitch), ld(vs, kf - g.pitch));
-                const double pf = phi_odd<T>(g, Df, inv_dt);
-                double px, py;
-                if (x_even) {
-                    py = phi_odd<T>(g, Dc.y, inv_dt);
-                    const double pn = phi_odd<T>(g, Dn.x, inv_dt), ps = phi_odd<T>(g, Dm.x, inv_dt);
+                const double Df = div_raw<T>(g, ld(us, kf + 1), ld(us, kf - 1), ld(vs, kf + g.pitch), ld(vs, kf - g.pitch));
+                if (!(has_mask && mask[kf])) pf = phi_odd<T>(g, Df, inv_dt);
+            }
+            double px = 0.0, py = 0.0;
+            if (x_even) {
+                if (yin && !mc.y) py = phi_odd<T>(g, Dc.y, inv_dt);
+                if (xin && !mc.x) {
+                    const double pn = mn.x ? 0.0 : phi_odd<T>(g, Dn.x, inv_dt), ps = mm.x ? 0.0 : phi_odd<T>(g, Dm.x, inv_dt);
                     px = (g.ax * (py + pf) + g.ay * (pn + ps) - (-Dc.x * inv_dt)) * g.dinv;
-                } else {
-                    px = phi_odd<T>(g, Dc.x, inv_dt);
-                    const double pn = phi_odd<T>(g, Dn.y, inv_dt), ps = phi_odd<T>(g, Dm.y, inv_dt);
+                }
+            } else {
+                if (xin && !mc.x) px = phi_odd<T>(g, Dc.x, inv_dt);
+                if (yin && !mc.y) {
+                    const double pn = mn.y ? 0.0 : phi_odd<T>(g, Dn.y, inv_dt), ps = mm.y ? 0.0 : phi_odd<T>(g, Dm.y, inv_dt);
                     py = (g.ax * (pf + px) + g.ay * (pn + ps) - (-Dc.y * inv_dt)) * g.dinv;
                 }
-                st2<T>(phi, k, px, py);
-                if (DIV) st2<T>(div_out, k, Dc.x, Dc.y);
-                if (ownx) { dabs = fmax(dabs, fabs(Dc.x)); ch = fmax(ch, fabs(px)); }
-                if (owny) { dabs = fmax(dabs, fabs(Dc.y)); ch = fmax(ch, fabs(py)); }
-                Dm = Dc; Dc = Dn; vm = vc; vc = vn; vn = vnn;
             }
+            st2<T>(phi, k, px, py);
+            if (DIV) st2<T>(div_out, k, Dc.x, Dc.y);
+            if (ownx) { dabs = fmax(dabs, fabs(Dc.x)); ch = fmax(ch, fabs(px)); }
+            if (owny) { dabs = fmax(dabs, fabs(Dc.y)); ch = fmax(ch, fabs(py)); }
+            Dm = Dc; Dc = Dn; vm = vc; vc = vn; vn = vnn; mm = mc; mc = mn;
         }
     }
     if (ctl) {
@@ -371,6 +405,11 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
             }
             for (int i = lo; i < hi; ++i, ro += g.pitch) {
                 // row i+1: raw velocity, psi row i+2 (exists unless i+1 is the border row, where no correction applies)
+                if (inb && i + FPF < g.ny) {
+                    const long long kp = ro + FPF * g.pitch + c0;
+                    pf_l2(ua + kp); pf_l2(va + kp);
+                    if (PSI) pf_l2(psi + kp);
+                }
                 if (PSI) pn = (i + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
                 D2 fun, fvn;
                 apply_row(i + 1, ld2g<T>(ua, ro + g.pitch, c0, inb), ld2g<T>(va, ro + g.pitch, c0, inb), pm, pc, pn, fun, fvn);

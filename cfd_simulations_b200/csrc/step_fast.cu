@@ -324,7 +324,7 @@ __device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xf
 __device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
 
 template <typename T, bool PSI>
-__global__ void __launch_bounds__(FBT, 4)
+__global__ void __launch_bounds__(FBT, 3)
 k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
                 const T* __restrict__ psi, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm,
                 const uint8_t* __restrict__ mask, const double* __restrict__ y, double* __restrict__ ke_part,
@@ -336,63 +336,62 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
     const bool inb = c0 >= 0 && c0 + 1 < g.nx;
     const bool owner = inb && lane >= 1 && lane <= 30;
     FinAcc acc;
-    // warp-uniform: is any flag tile over the owned columns set?
-    bool flagged;
-    {
-        const int cA = min(own_c0, g.nx - 1), cB = min(own_c0 + FW_OWN, g.nx);
-        const int tx0 = cA / FT_W, tx1 = max(cB - 1, cA) / FT_W, ty0 = r0 / FT_H, ty1 = (r1 - 1) / FT_H;
-        const int w = tx1 - tx0 + 1, n = w * (ty1 - ty0 + 1);
-        int f = 0;
-        for (int t = lane; t < n; t += 32) f |= flags[(ty0 + t / w) * ntx + tx0 + t % w];
-        flagged = __any_sync(0xffffffffu, f != 0);
-    }
     if (own_c0 < g.nx) {
-        if (flagged) {
-            if (owner) {
-                for (int i = r0; i < r1; ++i)
-                    for (int c = c0; c < c0 + 2; ++c) {
-                        if (PSI) { const ApplyVel<T> vel{ua, va, psi}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
-                        else { const PlainVel<T> vel{ua, va}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
+        // warp-uniform: do the flag tiles over the owned columns (they are dilated by 2 cells) carry ibm / mask bits?
+        int f = 0;
+        {
+            const int cB = min(own_c0 + FW_OWN, g.nx);
+            const int tx0 = own_c0 / FT_W, tx1 = (cB - 1) / FT_W, ty0 = r0 / FT_H, ty1 = (r1 - 1) / FT_H;
+            const int w = tx1 - tx0 + 1, n = w * (ty1 - ty0 + 1);
+            for (int t = lane; t < n; t += 32) f |= flags[(ty0 + t / w) * ntx + tx0 + t % w];
+        }
+        const bool has_ibm = __any_sync(0xffffffffu, f & 1), has_mask = mask && __any_sync(0xffffffffu, f & 2);
+        const int cx = inb ? col_class(g, c0) : COL_COPY, cy = inb ? col_class(g, c0 + 1) : COL_COPY;
+        const bool inx = inb && cx == COL_INTERIOR, iny = inb && cy == COL_INTERIOR;
+        const bool ownx = owner && c0 >= g.own0 && c0 < g.own1, owny = owner && c0 + 1 >= g.own0 && c0 + 1 < g.own1;
+        const double i2dx = 1.0 / Rnd<T>::r(g.two_dx), i2dy = 1.0 / Rnd<T>::r(g.two_dy);
+        const double vmax = p.max_velocity, fs = ctl->fs, pert = ctl->pert_scale, phase = ctl->phase;
+        const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+        // wall rows: u = v = 0 (v5.py:357-360); they count in the energy mean
+        if (owner && r0 == 0) { st2<T>(u, c0, 0.0, 0.0); st2<T>(v, c0, 0.0, 0.0); acc.cnt += (ownx ? 1 : 0) + (owny ? 1 : 0); }
+        if (owner && r1 == g.ny) {
+            const long long kk = (long long)(g.ny - 1) * g.pitch + c0;
+            st2<T>(u, kk, 0.0, 0.0); st2<T>(v, kk, 0.0, 0.0); acc.cnt += (ownx ? 1 : 0) + (owny ? 1 : 0);
+        }
+        // velocity of one row after the pending correction, from its stored values and three psi rows (all lanes:
+        // the x-neighbours of psi come from shuffles)
+        auto apply_row = [&](int row, const D2& ur, const D2& vr, const D2& pS, const D2& pC, const D2& pN, D2& fu, D2& fv) {
+            fu = ur; fv = vr;
+            if (PSI) {
+                const double pW = shfl_up1(pC.y), pE = shfl_dn1(pC.x);
+                if (row >= 1 && row < g.ny - 1) {
+                    if (inx) {
+                        fu.x = Rnd<T>::r(ur.x - Rnd<T>::r((pC.y - pW) * g.hdx));
+                        fv.x = Rnd<T>::r(vr.x - Rnd<T>::r((pN.x - pS.x) * g.hdy));
                     }
-            }
-        } else {
-            // column predicates
-            const bool inx = inb && c0 >= 1 && g.jg0 + c0 >= 1 && g.jg0 + c0 < g.nxg - 1;                       // c0 interior
-            const bool iny = inb && c0 + 1 < g.nx - 1 && g.jg0 + c0 + 1 >= 1 && g.jg0 + c0 + 1 < g.nxg - 1;    // c0+1 interior
-            const bool plain = owner && c0 >= 2 && c0 + 3 < g.nx && g.jg0 + c0 >= 2 && g.jg0 + c0 + 3 < g.nxg;
-            const bool ownx = c0 >= g.own0 && c0 < g.own1, owny = c0 + 1 >= g.own0 && c0 + 1 < g.own1;
-            const double i2dx = 1.0 / Rnd<T>::r(g.two_dx), i2dy = 1.0 / Rnd<T>::r(g.two_dy);
-            const double vmax = p.max_velocity;
-            const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
-            // general per-cell code for the wall rows and for owned cells of non-plain lanes
-            auto general_cell = [&](int i, int c) {
-                if (PSI) { const ApplyVel<T> vel{ua, va, psi}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
-                else { const PlainVel<T> vel{ua, va}; finalize_point<T>(g, p, ctl, vel, u, v, ibm, mask, y, i, c, acc); }
-            };
-            if (owner && r0 == 0) { general_cell(0, c0); general_cell(0, c0 + 1); }
-            if (owner && r1 == g.ny) { general_cell(g.ny - 1, c0); general_cell(g.ny - 1, c0 + 1); }
-            // corrected velocity of one row from its raw values and three psi rows (all lanes, convergent: shuffles)
-            auto apply_row = [&](int row, const D2& ur, const D2& vr, const D2& pS, const D2& pC, const D2& pN, D2& fu, D2& fv) {
-                fu = ur; fv = vr;
-                if (PSI) {
-                    const double pW = shfl_up1(pC.y), pE = shfl_dn1(pC.x);
-                    if (row >= 1 && row < g.ny - 1) {
-                        if (inx) {
-                            fu.x = Rnd<T>::r(ur.x - Rnd<T>::r((pC.y - pW) * g.hdx));
-                            fv.x = Rnd<T>::r(vr.x - Rnd<T>::r((pN.x - pS.x) * g.hdy));
-                        }
-                        if (iny) {
-                            fu.y = Rnd<T>::r(ur.y - Rnd<T>::r((pE - pC.x) * g.hdx));
-                            fv.y = Rnd<T>::r(vr.y - Rnd<T>::r((pN.y - pS.y) * g.hdy));
-                        }
+                    if (iny) {
+                        fu.y = Rnd<T>::r(ur.y - Rnd<T>::r((pE - pC.x) * g.hdx));
+                        fv.y = Rnd<T>::r(vr.y - Rnd<T>::r((pN.y - pS.y) * g.hdy));
                     }
                 }
-            };
+            }
+        };
+        // IBM multiplier 1 - ibm*fs of one row (1 where ibm <= 0; exact: x*1.0 == x)
+        auto mult_row = [&](long long ro_) {
+            D2 m = {1.0, 1.0};
+            if (has_ibm && inb) {
+                const double2 t = *reinterpret_cast<const double2*>(ibm + ro_ + c0);
+                if (t.x > 0) m.x = 1.0 - t.x * fs;
+                if (t.y > 0) m.y = 1.0 - t.y * fs;
+            }
+            return m;
+        };
+        if (lo < hi) {
             long long ro = (long long)lo * g.pitch;
             D2 pm = {0, 0}, pc = {0, 0}, pn = {0, 0};     // psi rows (i), (i+1), (i+2) while row i is processed
-            D2 fum, fvm, fuc, fvc;
+            D2 gum = {0, 0}, fvm, fuc, fvc, mc;
             {   // rows lo-1 and lo
-                D2 pmm = {0, 0};
+                D2 pmm = {0, 0}, fum;
                 if (PSI) {
                     if (lo - 2 >= 0) pmm = ld2g<T>(psi, ro - 2 * g.pitch, c0, inb);
                     pm = ld2g<T>(psi, ro - g.pitch, c0, inb);
@@ -402,47 +401,74 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
                 apply_row(lo - 1, ld2g<T>(ua, ro - g.pitch, c0, inb), ld2g<T>(va, ro - g.pitch, c0, inb), pmm, pm, pc, fum, fvm);
                 apply_row(lo, ld2g<T>(ua, ro, c0, inb), ld2g<T>(va, ro, c0, inb), pm, pc, pn, fuc, fvc);
                 pm = pc; pc = pn;      // now pm = psi(lo), pc = psi(lo+1)
+                if (lo - 1 >= 1) {     // processed u of row lo-1 (0 on the wall row); only interior columns use it
+                    const D2 mm = mult_row(ro - g.pitch);
+                    gum.x = Rnd<T>::r(fum.x * mm.x); gum.y = Rnd<T>::r(fum.y * mm.y);
+                }
+                mc = mult_row(ro);
             }
+            // software pipeline: stored values of row i+1 (and psi row i+2) are loaded one iteration ahead
+            D2 urn = ld2g<T>(ua, ro + g.pitch, c0, inb), vrn = ld2g<T>(va, ro + g.pitch, c0, inb);
+            if (PSI) pn = (lo + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
+            D2 mn = (lo + 1 < g.ny - 1) ? mult_row(ro + g.pitch) : D2{1.0, 1.0};
             for (int i = lo; i < hi; ++i, ro += g.pitch) {
-                // row i+1: raw velocity, psi row i+2 (exists unless i+1 is the border row, where no correction applies)
+                // issue the loads of the NEXT iteration: stored row i+2, psi row i+3, ibm row i+2
+                D2 urn2 = {0, 0}, vrn2 = {0, 0}, pn2 = {0, 0}, mn2 = {1.0, 1.0};
+                if (i + 1 < hi) {
+                    urn2 = ld2g<T>(ua, ro + 2 * g.pitch, c0, inb); vrn2 = ld2g<T>(va, ro + 2 * g.pitch, c0, inb);
+                    if (PSI && i + 3 < g.ny) pn2 = ld2g<T>(psi, ro + 3 * g.pitch, c0, inb);
+                    if (i + 2 < g.ny - 1) mn2 = mult_row(ro + 2 * g.pitch);
+                }
                 if (inb && i + FPF < g.ny) {
                     const long long kp = ro + FPF * g.pitch + c0;
                     pf_l2(ua + kp); pf_l2(va + kp);
                     if (PSI) pf_l2(psi + kp);
                 }
-                if (PSI) pn = (i + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
                 D2 fun, fvn;
-                apply_row(i + 1, ld2g<T>(ua, ro + g.pitch, c0, inb), ld2g<T>(va, ro + g.pitch, c0, inb), pm, pc, pn, fun, fvn);
-                const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), fvW = shfl_up1(fvc.y), fvE = shfl_dn1(fvc.x);
-                if (plain) {
-                    const double dx_ = Rnd<T>::r((fuc.y - fuW) * g.hdx + (fvn.x - fvm.x) * g.hdy);
-                    const double dy_ = Rnd<T>::r((fuE - fuc.x) * g.hdx + (fvn.y - fvm.y) * g.hdy);
-                    const double wx = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvc.y - fvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.x - fum.x) * i2dy));
-                    const double wy = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvE - fvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.y - fum.y) * i2dy));
-                    const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.x * fuc.x) + Rnd<T>::r(fvc.x * fvc.x)));
-                    const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.y * fuc.y) + Rnd<T>::r(fvc.y * fvc.y)));
-                    const double cux = fmin(fmax(fuc.x, -vmax), vmax), cuy = fmin(fmax(fuc.y, -vmax), vmax);
-                    const double cvx = fmin(fmax(fvc.x, -vmax), vmax), cvy = fmin(fmax(fvc.y, -vmax), vmax);
+                apply_row(i + 1, urn, vrn, pm, pc, pn, fun, fvn);
+                // BC (v5.py:349-360) + IBM (v5.py:228-237) of row i, pointwise
+                D2 guc = fuc, gvc = fvc;
+                if (cx == COL_INFLOW) { guc.x = Rnd<T>::r(inflow_u(p.V_inf, p.y_max, y[i], pert, phase)); gvc.x = 0.0; }
+                if (cy == COL_OUTFLOW) { guc.y = fuc.x; gvc.y = fvc.x; }     // copies column nx-2 (before its IBM)
+                if (has_ibm) {
+                    guc.x = Rnd<T>::r(guc.x * mc.x); gvc.x = Rnd<T>::r(gvc.x * mc.x);
+                    guc.y = Rnd<T>::r(guc.y * mc.y); gvc.y = Rnd<T>::r(gvc.y * mc.y);
+                }
+                // processed u of row i+1 (north neighbour of the vorticity stencil): 0 on the wall row
+                D2 gun = {0, 0};
+                if (i + 1 < g.ny - 1) { gun.x = Rnd<T>::r(fun.x * mn.x); gun.y = Rnd<T>::r(fun.y * mn.y); }
+                const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), gvW = shfl_up1(gvc.y), gvE = shfl_dn1(gvc.x);
+                if (owner) {
+                    uchar2 mk = make_uchar2(0, 0);
+                    if (has_mask) mk = *reinterpret_cast<const uchar2*>(mask + ro + c0);
+                    if (inx && ownx) {
+                        acc.dmax = fmax(acc.dmax, fabs(Rnd<T>::r((fuc.y - fuW) * g.hdx + (fvn.x - fvm.x) * g.hdy)));
+                        if (!mk.x) acc.wmax = fmax(acc.wmax, fabs(Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvc.y - gvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.x - gum.x) * i2dy))));
+                    }
+                    if (iny && owny) {
+                        acc.dmax = fmax(acc.dmax, fabs(Rnd<T>::r((fuE - fuc.x) * g.hdx + (fvn.y - fvm.y) * g.hdy)));
+                        if (!mk.y) acc.wmax = fmax(acc.wmax, fabs(Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvE - gvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.y - gum.y) * i2dy))));
+                    }
+                    const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.x * guc.x) + Rnd<T>::r(gvc.x * gvc.x)));
+                    const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.y * guc.y) + Rnd<T>::r(gvc.y * gvc.y)));
+                    const double cux = fmin(fmax(guc.x, -vmax), vmax), cuy = fmin(fmax(guc.y, -vmax), vmax);
+                    const double cvx = fmin(fmax(gvc.x, -vmax), vmax), cvy = fmin(fmax(gvc.y, -vmax), vmax);
                     // np.clip propagates NaN; fmin/fmax would drop it
-                    st2<T>(u, ro + c0, fuc.x == fuc.x ? cux : fuc.x, fuc.y == fuc.y ? cuy : fuc.y);
-                    st2<T>(v, ro + c0, fvc.x == fvc.x ? cvx : fvc.x, fvc.y == fvc.y ? cvy : fvc.y);
+                    st2<T>(u, ro + c0, guc.x == guc.x ? cux : guc.x, guc.y == guc.y ? cuy : guc.y);
+                    st2<T>(v, ro + c0, gvc.x == gvc.x ? cvx : gvc.x, gvc.y == gvc.y ? cvy : gvc.y);
                     if (ownx) {
-                        acc.dmax = fmax(acc.dmax, fabs(dx_)); acc.wmax = fmax(acc.wmax, fabs(wx));
                         if (ex == ex) { acc.e += ex; acc.cnt += 1; }
-                        if (!isfinite(ex)) acc.bad = 1;
+                        if (!isfinite(guc.x) || !isfinite(gvc.x)) acc.bad = 1;
                         acc.mu = fmax(acc.mu, fabs(cux)); acc.mv = fmax(acc.mv, fabs(cvx));
                     }
                     if (owny) {
-                        acc.dmax = fmax(acc.dmax, fabs(dy_)); acc.wmax = fmax(acc.wmax, fabs(wy));
                         if (ey == ey) { acc.e += ey; acc.cnt += 1; }
-                        if (!isfinite(ey)) acc.bad = 1;
+                        if (!isfinite(guc.y) || !isfinite(gvc.y)) acc.bad = 1;
                         acc.mu = fmax(acc.mu, fabs(cuy)); acc.mv = fmax(acc.mv, fabs(cvy));
                     }
-                } else if (owner) {
-                    general_cell(i, c0); general_cell(i, c0 + 1);
                 }
-                fum = fuc; fvm = fvc; fuc = fun; fvc = fvn;
-                pm = pc; pc = pn;
+                gum = guc; fvm = fvc; fuc = fun; fvc = fvn; mc = mn; mn = mn2;
+                pm = pc; pc = pn; pn = pn2; urn = urn2; vrn = vrn2;
             }
         }
     }

@@ -536,7 +536,8 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
     Geom g = make_geom(h->g.ny, h->g.nx, h->g.pitch, dx, dy, h->g.jg0, h->g.nxg);
     const size_t fb = (size_t)g.ny * g.nx * h->es;
     launch_poisson_reset(h->ctl, s);
-    int done_iters = 0;
+    int done_iters = 0, tb_done_iters = -1;
+    double tb_last_change = 0.0;
     if (mode == B200CFD_POISSON_JACOBI) {
         const double k = dx * dx / dt;
         int it = 0;
@@ -556,12 +557,18 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
         const double inv_dt = 1.0 / dt;
         const bool check = (tol > 0.0);
         int it = 0;
-        if (!check && temporal_depth != 1 && iters >= 2) {
-            int rc = poisson_tb_rbsor(&h->tb, dtp, g, h->n_sm, phi, rhs_div, mask, inv_dt, omega, iters, temporal_depth, &it, s);
+        double tb_last = 0.0;
+        bool tb_ran = false;
+        if (temporal_depth != 1 && iters >= 2) {
+            // TMA temporally blocked passes; in tolerance mode they stop at exactly the iteration the sequential
+            // algorithm stops at (per-iteration max|dphi| slots), synchronising once per pass
+            int rc = poisson_tb_rbsor(&h->tb, dtp, g, h->n_sm, phi, rhs_div, mask, inv_dt, omega, iters, temporal_depth, &it, s,
+                                      check ? tol : 0.0, &tb_last);
             if (rc < 0) return fail(h, B200CFD_ECUDA, "temporally blocked red-black: %s", poisson_tb_error());
+            tb_ran = it > 0;
         }
         const int chunk = 32;
-        while (it < iters) {
+        while (!tb_ran && it < iters) {
             const int m = (iters - it < chunk) ? iters - it : chunk;
             for (int q = 0; q < m; ++q) {
                 launch_rbgs_color(dtp, g, phi, rhs_div, mask, inv_dt, omega, 0, h->ctl, tol, 0, s);
@@ -576,8 +583,15 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
             }
         }
         done_iters = it;
+        if (tb_ran) { tb_done_iters = it; tb_last_change = tb_last; }
     }
     CHECK_LAUNCH(h);
+    if (mode != B200CFD_POISSON_JACOBI && tb_done_iters >= 0) {
+        if (iters_done) *iters_done = tb_done_iters;
+        if (last_change) *last_change = tb_last_change;
+        if (iters_done || last_change) CU(h, cudaStreamSynchronize(s));
+        return B200CFD_OK;
+    }
     if (iters_done || last_change) {
         StepCtl c;
         CU(h, cudaMemcpyAsync(&c, h->ctl, sizeof(StepCtl), cudaMemcpyDeviceToHost, s));

@@ -12,5 +12,6 @@ void poisson_tb_destroy(PoissonTB* tb);
 int poisson_tb_jacobi(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
                       double dx2_over_dt, int sweeps, int depth, int* iters_done, cudaStream_t s);
 int poisson_tb_rbsor(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
-                     double inv_dt, double omega, int iters, int depth, int* iters_done, cudaStream_t s);
+                     double inv_dt, double omega, int iters, int depth, int* iters_done, cudaStream_t s, double tol = 0.0,
+                     double* last_change = nullptr);   // tol > 0: stops at the first iteration with max|dphi| < tol (synchronises per pass)
 }  // namespace b200cfd

@@ -44,6 +44,27 @@ class StepScalars(C.Structure):
         "max_abs_v", "poisson_iters", "poisson_change", "nonfinite", "step")]
 
 
+class EulerConfig(C.Structure):
+    """b200cfd_euler_config (include/b200cfd_euler.h) — mirrors ShockwaveConfig, v1_shock.py:35-67."""
+    _fields_ = [
+        ("nx", C.c_int32), ("ny", C.c_int32), ("solver_type", C.c_int32), ("n_reflect", C.c_int32),
+        ("rank", C.c_int32), ("nranks", C.c_int32), ("halo_lo", C.c_int32), ("halo_hi", C.c_int32),
+        ("exact_division", C.c_int32), ("reserved", C.c_int32),
+        ("gamma", C.c_double), ("epsilon", C.c_double), ("max_val", C.c_double), ("cfl", C.c_double),
+        ("dx", C.c_double), ("dy", C.c_double), ("rho_inf", C.c_double), ("u_inf", C.c_double), ("p_inf", C.c_double),
+    ]
+
+
+# every symbol include/b200cfd_euler.h declares
+EULER_EXPORTS = [
+    "b200cfd_euler_last_error", "b200cfd_euler_create", "b200cfd_euler_destroy", "b200cfd_euler_bind",
+    "b200cfd_euler_step", "b200cfd_euler_step_host", "b200cfd_euler_step_begin", "b200cfd_euler_step_end",
+    "b200cfd_euler_reduction_ptr", "b200cfd_euler_reduction_len", "b200cfd_euler_local_speeds",
+    "b200cfd_euler_set_dt_from", "b200cfd_euler_state", "b200cfd_euler_fetch_dts", "b200cfd_euler_launches_per_step",
+    "b200cfd_euler_k_riemann", "b200cfd_euler_k_fluxes", "b200cfd_euler_k_update_state", "b200cfd_euler_k_compute_dt",
+    "b200cfd_euler_k_apply_bc",
+]
+
 # every symbol include/b200cfd.h declares (tests check the library exports all of them)
 EXPORTS = [
     "b200cfd_abi_version", "b200cfd_last_error", "b200cfd_device_count", "b200cfd_create", "b200cfd_destroy",
@@ -105,6 +126,28 @@ def load():
     lib.b200cfd_set_step_global.argtypes = [vp, i64, dbl, dbl, vp]
     lib.b200cfd_pack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
     lib.b200cfd_unpack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
+    # ---- include/b200cfd_euler.h ----
+    lib.b200cfd_euler_last_error.restype = C.c_char_p
+    lib.b200cfd_euler_last_error.argtypes = [vp]
+    lib.b200cfd_euler_create.argtypes = [C.POINTER(EulerConfig), i32, C.POINTER(vp)]
+    lib.b200cfd_euler_destroy.argtypes = [vp]
+    lib.b200cfd_euler_bind.argtypes = [vp, vp, vp, vp, i64, vp]
+    lib.b200cfd_euler_step.argtypes = [vp, i32, i32, vp]
+    lib.b200cfd_euler_step_host.argtypes = [vp, vp, i32, i32, C.POINTER(dbl), vp]
+    lib.b200cfd_euler_step_begin.argtypes = [vp, vp]
+    lib.b200cfd_euler_step_end.argtypes = [vp, vp, vp]
+    lib.b200cfd_euler_reduction_ptr.argtypes = [vp]
+    lib.b200cfd_euler_reduction_ptr.restype = vp
+    lib.b200cfd_euler_local_speeds.argtypes = [vp, vp]
+    lib.b200cfd_euler_set_dt_from.argtypes = [vp, vp, i64, vp]
+    lib.b200cfd_euler_state.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_int32), C.POINTER(dbl), C.POINTER(i64), vp]
+    lib.b200cfd_euler_fetch_dts.argtypes = [vp, i64, i32, C.POINTER(dbl), vp]
+    lib.b200cfd_euler_launches_per_step.argtypes = [vp]
+    lib.b200cfd_euler_k_riemann.argtypes = [vp, vp, i32, i32, i32, dbl, dbl, dbl, vp, vp]
+    lib.b200cfd_euler_k_fluxes.argtypes = [vp, i32, dbl, dbl, dbl, vp, vp, vp]
+    lib.b200cfd_euler_k_update_state.argtypes = [vp, vp, vp, vp, dbl, vp, vp]
+    lib.b200cfd_euler_k_compute_dt.argtypes = [vp, vp, C.POINTER(dbl), vp]
+    lib.b200cfd_euler_k_apply_bc.argtypes = [vp, vp, vp, vp]
     _lib = lib
     return lib
 
@@ -113,3 +156,9 @@ def check(rc: int, handle=None):
     if rc != 0:
         msg = load().b200cfd_last_error(handle)
         raise B200CFDError(f"libb200cfd error {rc}: {msg.decode() if msg else ''}")
+
+
+def check_euler(rc: int, handle=None):
+    if rc != 0:
+        msg = load().b200cfd_euler_last_error(handle)
+        raise B200CFDError(f"libb200cfd (euler) error {rc}: {msg.decode() if msg else ''}")

@@ -59,3 +59,34 @@ def test_product_package_never_imports_oracle():
     for f in (ROOT / "cfd_simulations_b200").rglob("*.py"):
         src = f.read_text()
         assert "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_euler_exports_and_struct_layout():
+    lib = _lib.load()
+    txt = (ROOT / "include" / "b200cfd_euler.h").read_text()
+    declared = set(re.findall(r"\b(b200cfd_euler_[a-z0-9_]+)\s*\(", txt))
+    assert declared == set(_lib.EULER_EXPORTS)
+    assert not [s for s in declared if not hasattr(lib, s)]
+    body = txt[txt.index("typedef struct b200cfd_euler_config {"):txt.index("} b200cfd_euler_config;")]
+    names = []
+    for line in body.splitlines()[1:]:
+        line = line.split("/*")[0].strip()
+        m = re.match(r"(int32_t|double)\s+([^;]+);", line)
+        if m:
+            names += [(n.strip(), m.group(1)) for n in m.group(2).split(",")]
+    got = [(n, "int32_t" if t is C.c_int32 else "double") for n, t in _lib.EulerConfig._fields_]
+    assert got == names
+
+
+def test_euler_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    lib = _lib.load()
+    h = C.c_void_p()
+    cfg = _lib.EulerConfig(nx=16, ny=16, nranks=1, dx=0.1, dy=0.1, gamma=1.4)
+    assert lib.b200cfd_euler_create(C.byref(cfg), 0, C.byref(h)) == -2
+    assert b"no CPU fallback" in lib.b200cfd_euler_last_error(None)
+    from cfd_simulations_b200.shockwave import ShockwaveConfig, ShockwaveSolver
+    with pytest.raises(_lib.B200CFDError):
+        ShockwaveSolver(ShockwaveConfig(nx=32, ny=16))

@@ -114,6 +114,24 @@ class HaloExchanger:
                 self.unpack(f, p.own1, p.halo_right, self.rbuf_r[k])
 
 
+def exchange_halo_rows(buf, rank, nranks, halo_lo, halo_hi, group=None):
+    """Euler x-slabs (shockwave.py): x is the SLOW axis of the (rows, ny, 4) state, so a halo is one contiguous row.
+    Row 0 / row -1 of `buf` are the halo rows (when present); they are refreshed from the neighbour's outermost owned
+    row (its row 1 / row -2 ... i.e. index halo_lo / -1 - halo_hi) with one batched send/recv per neighbour."""
+    ops = []
+    n = buf.shape[0]
+    if halo_lo:
+        ops.append(dist.P2POp(dist.irecv, buf[0], rank - 1, group))
+        ops.append(dist.P2POp(dist.isend, buf[halo_lo], rank - 1, group))
+    if halo_hi:
+        ops.append(dist.P2POp(dist.irecv, buf[n - 1], rank + 1, group))
+        ops.append(dist.P2POp(dist.isend, buf[n - 1 - halo_hi], rank + 1, group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return 2 * buf[0].numel() * buf.element_size() * (int(bool(halo_lo)) + int(bool(halo_hi)))
+
+
 class _DevPtr:
     """Expose a raw device pointer to torch (zero-copy) through __cuda_array_interface__."""
 

@@ -82,6 +82,11 @@ class ShockwaveSolver:
             self._red = device_view(self._lib.b200cfd_euler_reduction_ptr(self._h), 4, dev)
         self._bind(0)
 
+    def _init_local(self, config, device, nranks, rank, U0, device_view, **kw):
+        """LocalShockSlabs: the constructor without its collective (the caller reduces over the slabs itself)."""
+        self._collectives = False
+        ShockwaveSolver.__init__(self, config, device=device, nranks=nranks, rank=rank, U0=U0, **kw)
+
     # ---- plumbing -------------------------------------------------------------------------------------------------
     def _bind(self, step):
         a, b = self._buf[self._cur], self._buf[self._cur ^ 1]
@@ -89,26 +94,15 @@ class ShockwaveSolver:
                                                  _sp(self.device)), self._h)
         self._buf = [a, b]
         self._cur = 0
-        if self._nranks > 1:
+        if self._nranks > 1 and getattr(self, "_collectives", True):
             import torch.distributed as dist
             dist.all_reduce(self._red, op=dist.ReduceOp.MAX, group=self._group)
             check_euler(self._lib.b200cfd_euler_set_dt_from(self._h, self._red.data_ptr(), int(step), _sp(self.device)), self._h)
         self._calls = self._fetched = int(step)
 
     def _exchange_halos(self, buf):
-        """Refresh the halo rows of `buf` from the neighbours' outermost owned rows (contiguous ny*4 floats each)."""
-        import torch.distributed as dist
-        ops = []
-        n = buf.shape[0]
-        if self._hlo:
-            ops.append(dist.P2POp(dist.irecv, buf[0], self._rank - 1, self._group))
-            ops.append(dist.P2POp(dist.isend, buf[1], self._rank - 1, self._group))
-        if self._hhi:
-            ops.append(dist.P2POp(dist.irecv, buf[n - 1], self._rank + 1, self._group))
-            ops.append(dist.P2POp(dist.isend, buf[n - 2], self._rank + 1, self._group))
-        if ops:
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()
+        from .multigpu import exchange_halo_rows
+        exchange_halo_rows(buf, self._rank, self._nranks, self._hlo, self._hhi, self._group)
 
     def advance(self, n_steps: int):
         """n x time_step() with the state and dt resident in HBM (no host round trip)."""
@@ -210,6 +204,57 @@ class ShockwaveSolver:
             self.close()
         except Exception:
             pass
+
+
+class LocalShockSlabs:
+    """All x-slabs of a decomposition stepped in lockstep inside ONE process on ONE GPU (no NCCL): the all_reduce is a
+    torch.maximum over the slabs' reduction vectors and the halo refresh is a row copy.  Same kernels, same halo rows,
+    same reduction path as the multi-process run: it makes the decomposition testable on a single-GPU box."""
+
+    def __init__(self, config, nslabs, device=0, U0=None, **kw):
+        from .multigpu import device_view
+        self.config = config
+        self.slabs = []
+        for r in range(nslabs):
+            s = ShockwaveSolver.__new__(ShockwaveSolver)
+            s._local_emulation = True
+            self.slabs.append(s)
+        # construct each slab without collectives: nranks > 1 but the reductions are done here
+        for r, s in enumerate(self.slabs):
+            s._init_local(config, device, nslabs, r, U0, device_view, **kw)
+        self._reduce_and(lambda s, red: check_euler(
+            s._lib.b200cfd_euler_set_dt_from(s._h, red.data_ptr(), 0, _sp(s.device)), s._h))
+
+    def _reduce_and(self, fn):
+        red = torch.stack([s._red for s in self.slabs]).max(dim=0).values
+        for s in self.slabs:
+            fn(s, red)
+
+    def advance(self, n_steps):
+        S = self.slabs
+        for _ in range(int(n_steps)):
+            for s in S:
+                check_euler(s._lib.b200cfd_euler_step_begin(s._h, _sp(s.device)), s._h)
+                s._cur ^= 1
+            for a, b in zip(S[:-1], S[1:]):          # a holds the rows just below b's
+                ua, ub = a._buf[a._cur], b._buf[b._cur]
+                ub[0].copy_(ua[ua.shape[0] - 2])
+                ua[ua.shape[0] - 1].copy_(ub[1])
+            self._reduce_and(lambda s, red: check_euler(
+                s._lib.b200cfd_euler_step_end(s._h, red.data_ptr(), _sp(s.device)), s._h))
+            for s in S:
+                s._calls += 1
+
+    def gather(self):
+        return np.concatenate([s.U for s in self.slabs], axis=0)
+
+    @property
+    def dts(self):
+        return self.slabs[0].dts
+
+    def close(self):
+        for s in self.slabs:
+            s.close()
 
 
 # ---- module-level functions of the reference (v1_shock.py:84-223) on NumPy arrays, computed on the GPU ---------------

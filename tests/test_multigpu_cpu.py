@@ -81,3 +81,51 @@ def test_halo_exchange_gloo(world):
         p.join(120)
         assert p.exitcode == 0
     assert all(out[r] for r in range(world))
+
+
+# ---- Euler x-slabs (shockwave.py): rows are the slow axis, a halo is one contiguous row ----
+def test_euler_row_split_covers_rows():
+    from cfd_simulations_b200.shockwave import row_split
+    for nx, n in ((400, 1), (400, 3), (16384 * 8, 8), (1031, 4)):
+        r = [row_split(nx, n, k) for k in range(n)]
+        assert r[0][0] == 0 and r[-1][1] == nx
+        assert all(a[1] == b[0] for a, b in zip(r[:-1], r[1:]))
+        assert max(b - a for a, b in r) - min(b - a for a, b in r) <= 1
+
+
+def _row_worker(rank, world, port, nx, ny, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from cfd_simulations_b200.shockwave import row_split
+        i0, i1 = row_split(nx, world, rank)
+        hlo, hhi = int(rank > 0), int(rank < world - 1)
+        glob = np.arange(nx * ny * 4, dtype=np.float32).reshape(nx, ny, 4)
+        loc = torch.from_numpy(glob[i0 - hlo:i1 + hhi].copy())
+        if hlo:
+            loc[0] = -1.0
+        if hhi:
+            loc[-1] = -1.0
+        nbytes = multigpu.exchange_halo_rows(loc, rank, world, hlo, hhi)
+        ok = np.array_equal(loc.numpy(), glob[i0 - hlo:i1 + hhi]) and nbytes == 2 * ny * 16 * (hlo + hhi)
+        # the per-step reduction: all_reduce(MAX) of the 4-double vector
+        red = torch.tensor([1.0 + rank, 5.0 - rank, float(rank == 1), 0.0], dtype=torch.float64)
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        ok = ok and red.tolist() == [float(world), 5.0, 1.0, 0.0]
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_euler_halo_rows_gloo(world):
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_row_worker, args=(r, world, port, 23, 11, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert all(out[r] for r in range(world))

@@ -47,6 +47,7 @@ ALGO_BYTES = {
     "predictor": 16 + 16 + 8,            # R u,v  W u*,v* (+ W tau_supg, a reference attribute); ibm only in flagged tiles
     "poisson": 16 + 8 + 8,               # as executed: R u*,v*  W phi, div_u_star; mask only in flagged tiles
     "correct": 24 + 16,                  # R u*,v*,phi  W u,v
+    "poisson_correct": 16 + 8 + 8 + 16,  # K2 + K3 fused (default): R u*,v*  W phi, div_u_star, u, v
     "clean_sweep_1": 16 + 8,             # R u,v  W psi (psi_old = 0)
     "clean_apply_1": 24 + 16,            # R psi,u,v  W u,v
     "clean_sweep_2": 16 + 8 + 8,         # R u,v,psi_old  W psi

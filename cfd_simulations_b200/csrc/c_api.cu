@@ -39,6 +39,7 @@ struct b200cfd_handle {
     int n_part_used = 0;              // blocks of the finalize kernel in use
     uint8_t* flags = nullptr;         // tile-flag map of ibm / mask (step_fast.cu)
     bool fast = false;                // row-marching fast kernels applicable (decided when the fields are bound)
+    bool fuse_k23 = true;             // K2 + K3 in one kernel on the fast path (B200CFD_NO_FUSE_K23 turns it off)
     // caller-owned (bound) device memory
     void *u = nullptr, *v = nullptr, *phi = nullptr, *us = nullptr, *vs = nullptr, *div = nullptr, *tau = nullptr, *nu_t = nullptr;
     const double* ibm = nullptr;
@@ -181,6 +182,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
     {   // fast kernels: the default configuration on even, 16-byte aligned grids; tile flags of ibm / mask
         const void* ptrs[] = {u, v, phi, u_star, v_star, div_u_star, tau_supg, h->ua, h->va, h->psi[0], h->psi[1]};
         h->fast = h->cfg.use_supg && !h->cfg.use_les && fast_path_ok(h->g, ptrs, 11) && !getenv("B200CFD_NO_FAST");
+        h->fuse_k23 = !getenv("B200CFD_NO_FUSE_K23");
         CU(h, cudaSetDevice(h->device));
         launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
         CU(h, cudaDeviceSynchronize());
@@ -304,10 +306,19 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     else launch_predictor(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, nut, h->ibm, h->y, s);
     ++nl;
     prof_mark(h, "predictor", s, pi);
-    nl += enqueue_step_poisson(h, s);
-    prof_mark(h, "poisson", s, pi);
-    launch_correct(dt, h->g, h->ctl, h->us, h->vs, h->phi, h->ua, h->va, s); ++nl;
-    prof_mark(h, "correct", s, pi);
+    if (h->fast && h->fuse_k23 && c.poisson_mode == B200CFD_POISSON_AS_EXECUTED && c.omega == 1.0) {
+        // K2 + K3 in one pass: u*, v* are read once and phi is never re-read
+        launch_div_rb1_correct_fast(dt, h->g, h->us, h->vs, h->mask, h->phi, h->div, h->ua, h->va, h->phys.inv_cfg_dt, h->ctl,
+                                    h->flags, h->n_sm, s);
+        launch_rb1_close(h->ctl, c.pressure_tolerance, s);
+        nl += 2;
+        prof_mark(h, "poisson_correct", s, pi);
+    } else {
+        nl += enqueue_step_poisson(h, s);
+        prof_mark(h, "poisson", s, pi);
+        launch_correct(dt, h->g, h->ctl, h->us, h->vs, h->phi, h->ua, h->va, s); ++nl;
+        prof_mark(h, "correct", s, pi);
+    }
     // fast path: the last clean-divergence correction u,v -= grad(psi) is applied on the fly by the finalize kernel
     const bool defer = h->fast && c.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && c.clean_iters > 0;
     void* last_psi = nullptr;

@@ -15,6 +15,7 @@
 // formed on the fly from rotating rows of v and the current row of u, so psi_new costs
 // R(u, v, psi_old) + W(psi_new) = 32 B/cell in fp64 (24 B/cell in the first iteration where psi_old = 0).
 #include "kernels.h"
+#include <cstdlib>
 
 namespace b200cfd {
 
@@ -28,7 +29,50 @@ template <typename T> __device__ __forceinline__ double ldg0(const T* __restrict
 }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
-template <typename T, bool HAS_OLD>
+// One lane's CPL = 4 adjacent cells of a row.  The window origin is a multiple of 4 columns, so with a pitch that is a
+// multiple of 4 and 32-byte aligned fields (VEC) the four cells are ONE 256-bit (fp64: LDG.E.256, sm_100) or 128-bit
+// (fp32) access: a warp then touches each 32-byte sector once per row instead of four times (the scalar form is
+// L1-wavefront bound).  Lanes whose four columns are not all inside [0, nx) take the scalar, zero-filled path.
+template <typename T, int VEC> struct Row4;   // VEC: 0 scalar, 1 one 256-bit access, 2 two 128-bit accesses
+template <int VEC> struct Row4<double, VEC> {
+    static __device__ __forceinline__ void ld(const double* __restrict__ p, long long row_off, int c, int nx, double (&o)[CPL]) {
+        if (VEC == 1 && c >= 0 && c + CPL <= nx) {
+            asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+                         : "=d"(o[0]), "=d"(o[1]), "=d"(o[2]), "=d"(o[3]) : "l"(p + row_off + c));
+        } else if (VEC == 2 && c >= 0 && c + CPL <= nx) {
+            const double2 t0 = __ldg(reinterpret_cast<const double2*>(p + row_off + c));
+            const double2 t1 = __ldg(reinterpret_cast<const double2*>(p + row_off + c + 2));
+            o[0] = t0.x; o[1] = t0.y; o[2] = t1.x; o[3] = t1.y;
+        } else {
+#pragma unroll
+            for (int m = 0; m < CPL; ++m) o[m] = ldg0(p, row_off, c + m, nx);
+        }
+    }
+    static __device__ __forceinline__ void st(double* __restrict__ p, long long k, const double (&x)[CPL]) {
+        if (VEC == 1) {
+            asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p + k), "d"(x[0]), "d"(x[1]), "d"(x[2]), "d"(x[3]) : "memory");
+        } else {
+            *reinterpret_cast<double2*>(p + k) = make_double2(x[0], x[1]);
+            *reinterpret_cast<double2*>(p + k + 2) = make_double2(x[2], x[3]);
+        }
+    }
+};
+template <int VEC> struct Row4<float, VEC> {
+    static __device__ __forceinline__ void ld(const float* __restrict__ p, long long row_off, int c, int nx, double (&o)[CPL]) {
+        if (VEC && c >= 0 && c + CPL <= nx) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(p + row_off + c));
+            o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+        } else {
+#pragma unroll
+            for (int m = 0; m < CPL; ++m) o[m] = ldg0(p, row_off, c + m, nx);
+        }
+    }
+    static __device__ __forceinline__ void st(float* __restrict__ p, long long k, const double (&x)[CPL]) {
+        *reinterpret_cast<float4*>(p + k) = make_float4((float)x[0], (float)x[1], (float)x[2], (float)x[3]);
+    }
+};
+
+template <typename T, bool HAS_OLD, int VEC>
 __global__ void __launch_bounds__(32 * CWARPS)
 k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ pold,
               T* __restrict__ pnew) {
@@ -61,16 +105,21 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
     double ucur[CPL], vnext[CPL], pnext[CPL];
     {
         const long long rm = (long long)(iw0 - 1) * g.pitch, r0 = (long long)iw0 * g.pitch;
+        typedef Row4<T, VEC> R4;
+        R4::ld(v, rm, c0, nx, v_im1);
+        R4::ld(v, r0, c0, nx, v_i);
+        R4::ld(u, r0, c0, nx, ucur);
+        R4::ld(v, r0 + g.pitch, c0, nx, vnext);
+        if (HAS_OLD) {
+            // inflow guess for the rows above the window: psi_old there (exact 0 when iw0 == 1: border row)
+            R4::ld(pold, rm, c0, nx, xprev);
+            R4::ld(pold, r0, c0, nx, pcur);
+            R4::ld(pold, r0 + g.pitch, c0, nx, pnext);
+        }
 #pragma unroll
         for (int m = 0; m < CPL; ++m) {
-            v_im1[m] = ldg0(v, rm, c0 + m, nx);
-            v_i[m] = ldg0(v, r0, c0 + m, nx);
-            // inflow guess for the rows above the window: psi_old there (exact 0 when iw0 == 1: border row)
-            xprev[m] = (HAS_OLD && iw0 > 1 && colin[m]) ? ldg0(pold, rm, c0 + m, nx) : 0.0;
-            pcur[m] = HAS_OLD ? ldg0(pold, r0, c0 + m, nx) : 0.0;
-            ucur[m] = ldg0(u, r0, c0 + m, nx);
-            vnext[m] = ldg0(v, r0 + g.pitch, c0 + m, nx);
-            pnext[m] = HAS_OLD ? ldg0(pold, r0 + g.pitch, c0 + m, nx) : 0.0;
+            if (!(HAS_OLD && iw0 > 1 && colin[m])) xprev[m] = 0.0;
+            if (!HAS_OLD) { pcur[m] = 0.0; pnext[m] = 0.0; }
         }
     }
 
@@ -80,11 +129,15 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         {
             const bool more = (i + 1 < ie);
             const long long r1 = (long long)(i + 1) * g.pitch, r2 = r1 + g.pitch;
+            if (more) {                                            // row i+2 <= ny-1 because i+1 < ie <= ny-1
+                Row4<T, VEC>::ld(u, r1, c0, nx, un_);
+                Row4<T, VEC>::ld(v, r2, c0, nx, vn2);
+                if (HAS_OLD) Row4<T, VEC>::ld(pold, r2, c0, nx, pn2);
+            }
 #pragma unroll
             for (int m = 0; m < CPL; ++m) {
-                un_[m] = more ? ldg0(u, r1, c0 + m, nx) : 0.0;
-                vn2[m] = more ? ldg0(v, r2, c0 + m, nx) : 0.0;     // row i+2 <= ny-1 because i+1 < ie <= ny-1
-                pn2[m] = (HAS_OLD && more) ? ldg0(pold, r2, c0 + m, nx) : 0.0;
+                if (!more) { un_[m] = 0.0; vn2[m] = 0.0; }
+                if (!(HAS_OLD && more)) pn2[m] = 0.0;
             }
             const int ip = i + CPFD;
             if (ip < ie && c0 >= 0 && c0 < nx) {
@@ -132,10 +185,14 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         // ---- store owned cells
         if (i >= is) {
             const long long ro = (long long)i * g.pitch;
+            if (VEC && c0 >= js && c0 + CPL <= je) {
+                Row4<T, VEC>::st(pnew, ro + c0, x);
+            } else {
 #pragma unroll
-            for (int m = 0; m < CPL; ++m) {
-                const int c = c0 + m;
-                if (c >= js && c < je) pnew[ro + c] = (T)x[m];
+                for (int m = 0; m < CPL; ++m) {
+                    const int c = c0 + m;
+                    if (c >= js && c < je) pnew[ro + c] = (T)x[m];
+                }
             }
         }
         // ---- rotate
@@ -164,6 +221,12 @@ k_clean_apply(Geom g, T* __restrict__ u, T* __restrict__ v, const T* __restrict_
     v[k] = (T)((double)v[k] - gy);
 }
 
+// developer tuning knob (environment), read once per process
+static int tune_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
+}
+
 static int apron_for(double ratio, int bits) {
     // smallest L with ratio^L <= 2^-bits
     if (!(ratio > 0.0)) return 1;
@@ -188,7 +251,7 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     const int ncols = g.nx - 2, nrows = g.ny - 2;
     cp.n_strips = (ncols + cp.strip_w - 1) / cp.strip_w;
     // enough tiles for ~8 warps per SM, tile height in [32, 512]
-    const int want = 8 * n_sm;
+    const int want = tune_int("B200CFD_CLEAN_WARPS_PER_SM", 8) * n_sm;
     int nt = (want + cp.n_strips - 1) / cp.n_strips;
     int th = (nrows + nt - 1) / (nt > 0 ? nt : 1);
     if (th < 32) th = 32;
@@ -199,18 +262,34 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     return cp;
 }
 
+template <typename T>
+static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void* u, const void* v, const void* psi_old,
+                                 void* psi_new, int nblk, cudaStream_t s) {
+    // vector path: the window origin 1 + s*strip_w - apron_h is a multiple of 4 by construction (clean_plan)
+    const size_t al = 4 * sizeof(T);
+    const bool vec = g.pitch % 4 == 0 && (cp.j_first - cp.apron_h) % 4 == 0 && cp.strip_w % 4 == 0 &&
+                     ((size_t)u % al) == 0 && ((size_t)v % al) == 0 && ((size_t)psi_old % al) == 0 && ((size_t)psi_new % al) == 0;
+    const T *up = (const T*)u, *vp = (const T*)v, *po = (const T*)psi_old;
+    T* pn = (T*)psi_new;
+    const int mode = vec ? tune_int("B200CFD_CLEAN_VEC", 0) : 0;
+#define SWEEP_LAUNCH(V)                                                                                   \
+    do {                                                                                                  \
+        if (po) k_clean_sweep<T, true, V><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, po, pn);            \
+        else k_clean_sweep<T, false, V><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, nullptr, pn);         \
+    } while (0)
+    if (mode == 1) SWEEP_LAUNCH(1);
+    else if (mode == 2) SWEEP_LAUNCH(2);
+    else SWEEP_LAUNCH(0);
+#undef SWEEP_LAUNCH
+}
+
 void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
                         const void* psi_old, void* psi_new, cudaStream_t s) {
     const int ntile = cp.n_strips * cp.n_tiles;
     const int nblk = (ntile + CWARPS - 1) / CWARPS;
     if (nblk <= 0) return;
-    if (dtype == 0) {
-        if (psi_old) k_clean_sweep<double, true><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, (const double*)u, (const double*)v, (const double*)psi_old, (double*)psi_new);
-        else k_clean_sweep<double, false><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, (const double*)u, (const double*)v, nullptr, (double*)psi_new);
-    } else {
-        if (psi_old) k_clean_sweep<float, true><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, (const float*)u, (const float*)v, (const float*)psi_old, (float*)psi_new);
-        else k_clean_sweep<float, false><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, (const float*)u, (const float*)v, nullptr, (float*)psi_new);
-    }
+    if (dtype == 0) launch_clean_sweep_t<double>(g, cp, u, v, psi_old, psi_new, nblk, s);
+    else launch_clean_sweep_t<float>(g, cp, u, v, psi_old, psi_new, nblk, s);
 }
 
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s) {

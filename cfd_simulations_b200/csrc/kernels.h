@@ -65,6 +65,10 @@ void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCt
                            const uint8_t* flags, int n_sm, cudaStream_t s);
 void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
                          void* div_out, double inv_dt, StepCtl* ctl, const uint8_t* flags, int n_sm, cudaStream_t s);
+// K2 + K3 fused (as executed, omega = 1): div, one red-black iteration, velocity correction, three maxima
+void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
+                                 void* div_out, void* ua, void* va, double inv_dt, StepCtl* ctl, const uint8_t* flags,
+                                 int n_sm, cudaStream_t s);
 int finalize_fast_num_partials(const Geom& g, int n_sm);
 void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
                           const void* psi_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,

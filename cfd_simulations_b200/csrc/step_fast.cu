@@ -512,4 +512,155 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
 #undef FF
 }
 
+// ------------------------------------------------------------------------------------------------
+// K2 + K3 fused: D = div(u*, v*), the ONE red-black iteration from phi = 0, and the velocity correction
+//   ua = u* - dt (phi_E - phi_W)/(2dx),  va = v* - dt (phi_N - phi_S)/(2dy),  max|grad phi|      v5.py:409-417
+// in one pass: u*, v* are read once (16 B/cell) instead of twice, phi is never re-read: 41 B/cell instead of 25 + 40.
+// Layout as the finalize kernel: one warp owns 60 columns of a 64-column window (2 per lane, lanes 0 / 31 are halo
+// lanes whose phi is only the x-neighbour of lanes 1 / 30), and marches down its rows with D of rows i-1, i, i+1 and
+// phi of rows i-2, i-1, i in registers; the correction of row i-1 is applied as soon as phi of row i exists.  A block
+// of rows [r0, r1) computes phi of rows r0-1 and r1 redundantly (they belong to the neighbouring blocks).
+// ------------------------------------------------------------------------------------------------
+template <typename T, bool DIV>
+__global__ void __launch_bounds__(FBT, 4)
+k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint8_t* __restrict__ mask,
+                       T* __restrict__ phi, T* __restrict__ div_out, T* __restrict__ ua, T* __restrict__ va,
+                       double inv_dt, StepCtl* __restrict__ ctl, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
+    const int own_c0 = blockIdx.x * FB_OWN + warp * FW_OWN;        // first column owned by this warp
+    const int c0 = own_c0 - 2 + 2 * lane;                          // this lane's two columns: c0, c0+1
+    const bool inb = c0 >= 0 && c0 + 1 < g.nx;
+    const bool owner = inb && lane >= 1 && lane <= 30;
+    double dabs = 0.0, ch = 0.0, gmax = 0.0;
+    if (own_c0 < g.nx) {
+        int f = 0;
+        {
+            const int cB = min(own_c0 + FW_OWN, g.nx);
+            const int tx0 = own_c0 / FT_W, tx1 = (cB - 1) / FT_W, ty0 = r0 / FT_H, ty1 = (r1 - 1) / FT_H;
+            const int w = tx1 - tx0 + 1, n = w * (ty1 - ty0 + 1);
+            for (int t = lane; t < n; t += 32) f |= flags[(ty0 + t / w) * ntx + tx0 + t % w];
+        }
+        const bool has_mask = mask && __any_sync(0xffffffffu, f & 2);
+        const bool xin = inb && col_class(g, c0) == COL_INTERIOR, yin = inb && col_class(g, c0 + 1) == COL_INTERIOR;
+        const bool ownx = owner && c0 >= g.own0 && c0 < g.own1, owny = owner && c0 + 1 >= g.own0 && c0 + 1 < g.own1;
+        const double dt = ctl->dt;
+        const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+        // wall rows: D = phi = 0, no gradient: ua = u*, va = v*
+        if (owner && r0 == 0) {
+            st2<T>(phi, c0, 0.0, 0.0); if (DIV) st2<T>(div_out, c0, 0.0, 0.0);
+            const D2 a = ld2<T>(us, c0), b = ld2<T>(vs, c0);
+            st2<T>(ua, c0, a.x, a.y); st2<T>(va, c0, b.x, b.y);
+        }
+        if (owner && r1 == g.ny) {
+            const long long kk = (long long)(g.ny - 1) * g.pitch + c0;
+            st2<T>(phi, kk, 0.0, 0.0); if (DIV) st2<T>(div_out, kk, 0.0, 0.0);
+            const D2 a = ld2<T>(us, kk), b = ld2<T>(vs, kk);
+            st2<T>(ua, kk, a.x, a.y); st2<T>(va, kk, b.x, b.y);
+        }
+        if (lo < hi) {                                             // warp-uniform
+            auto vrow = [&](int r) { return (inb && r >= 0 && r < g.ny) ? ld2<T>(vs, (long long)r * g.pitch + c0) : D2{0.0, 0.0}; };
+            auto urow = [&](int r) { return (inb && r >= 0 && r < g.ny) ? ld2<T>(us, (long long)r * g.pitch + c0) : D2{0.0, 0.0}; };
+            auto mrow = [&](int r) {
+                return (has_mask && inb && r >= 0 && r < g.ny) ? *reinterpret_cast<const uchar2*>(mask + (long long)r * g.pitch + c0)
+                                                               : make_uchar2(0, 0);
+            };
+            // D of row r from its u* pair (x-neighbours by shuffle; the two halo lanes load theirs) and v* of rows r+1, r-1
+            auto drow = [&](int r, const D2& uc, const D2& vN, const D2& vS) {
+                D2 d = {0.0, 0.0};
+                if (r >= 1 && r < g.ny - 1) {                       // warp-uniform
+                    double uW = shfl_up1(uc.y), uE = shfl_dn1(uc.x);
+                    const long long kr = (long long)r * g.pitch + c0;
+                    if (lane == 0 && xin) uW = ld(us, kr - 1);
+                    if (lane == 31 && yin) uE = ld(us, kr + 2);
+                    if (xin) d.x = div_raw<T>(g, uc.y, uW, vN.x, vS.x);
+                    if (yin) d.y = div_raw<T>(g, uE, uc.x, vN.y, vS.y);
+                }
+                return d;
+            };
+            // phi of row i after the red (odd) then black (even) colour of the first iteration from phi = 0
+            auto prow = [&](int i, const D2& Dm, const D2& Dc, const D2& Dn, uchar2 mm, uchar2 mc, uchar2 mn) {
+                D2 q = {0.0, 0.0};
+                if (i >= 1 && i < g.ny - 1) {                       // warp-uniform
+                    if (((i + g.jg0 + c0) & 1) == 0) {              // warp-uniform: .x cells are even, .y cells odd
+                        if (yin && !mc.y) q.y = phi_odd<T>(g, Dc.y, inv_dt);
+                        const double pW = shfl_up1(q.y);
+                        if (xin && !mc.x) {
+                            const double pn = mn.x ? 0.0 : phi_odd<T>(g, Dn.x, inv_dt), ps = mm.x ? 0.0 : phi_odd<T>(g, Dm.x, inv_dt);
+                            q.x = Rnd<T>::r((g.ax * (q.y + pW) + g.ay * (pn + ps) - (-Dc.x * inv_dt)) * g.dinv);
+                        }
+                    } else {
+                        if (xin && !mc.x) q.x = phi_odd<T>(g, Dc.x, inv_dt);
+                        const double pE = shfl_dn1(q.x);
+                        if (yin && !mc.y) {
+                            const double pn = mn.y ? 0.0 : phi_odd<T>(g, Dn.y, inv_dt), ps = mm.y ? 0.0 : phi_odd<T>(g, Dm.y, inv_dt);
+                            q.y = Rnd<T>::r((g.ax * (pE + q.x) + g.ay * (pn + ps) - (-Dc.y * inv_dt)) * g.dinv);
+                        }
+                    }
+                }
+                return q;
+            };
+            int i = lo - 1;
+            D2 v_m = vrow(i - 1), v_c = vrow(i), v_n = vrow(i + 1);
+            D2 u_m = {0.0, 0.0}, u_c = urow(i);
+            D2 Dm = drow(i - 1, urow(i - 1), v_c, vrow(i - 2));
+            D2 Dc = drow(i, u_c, v_n, v_m);
+            uchar2 mm = mrow(i - 1), mc = mrow(i);
+            D2 p_mm = {0.0, 0.0}, p_m = {0.0, 0.0};
+            // software pipeline: the rows the NEXT iteration consumes are requested one iteration ahead
+            D2 v_nn = vrow(i + 2), u_n = urow(i + 1);
+            uchar2 mn = mrow(i + 1);
+            for (; i <= hi; ++i) {
+                const long long k = (long long)i * g.pitch + c0;
+                if (inb && i + FPF < g.ny) { pf_l2(us + k + FPF * g.pitch); pf_l2(vs + k + FPF * g.pitch); }
+                const bool more = i < hi;
+                const D2 v_n3 = more ? vrow(i + 3) : D2{0.0, 0.0}, u_n2 = more ? urow(i + 2) : D2{0.0, 0.0};
+                const uchar2 mn2 = more ? mrow(i + 2) : make_uchar2(0, 0);
+                const D2 Dn = drow(i + 1, u_n, v_nn, v_c);
+                const D2 p_c = prow(i, Dm, Dc, Dn, mm, mc, mn);
+                if (owner && i >= lo && i < hi) {
+                    st2<T>(phi, k, p_c.x, p_c.y);
+                    if (DIV) st2<T>(div_out, k, Dc.x, Dc.y);
+                    if (ownx) { dabs = fmax(dabs, fabs(Dc.x)); ch = fmax(ch, fabs(p_c.x)); }
+                    if (owny) { dabs = fmax(dabs, fabs(Dc.y)); ch = fmax(ch, fabs(p_c.y)); }
+                }
+                if (i - 1 >= lo) {                                  // correct row i-1: phi rows i-2 (p_mm), i-1 (p_m), i (p_c)
+                    const double pW = shfl_up1(p_m.y), pE = shfl_dn1(p_m.x);
+                    double gxx = 0.0, gxy = 0.0, gyx = 0.0, gyy = 0.0;
+                    if (xin) { gxx = Rnd<T>::r((p_m.y - pW) * g.hdx); gyx = Rnd<T>::r((p_c.x - p_mm.x) * g.hdy); }
+                    if (yin) { gxy = Rnd<T>::r((pE - p_m.x) * g.hdx); gyy = Rnd<T>::r((p_c.y - p_mm.y) * g.hdy); }
+                    if (owner) {
+                        st2<T>(ua, k - g.pitch, axmy<T>(u_m.x, dt, gxx), axmy<T>(u_m.y, dt, gxy));
+                        st2<T>(va, k - g.pitch, axmy<T>(v_m.x, dt, gyx), axmy<T>(v_m.y, dt, gyy));
+                    }
+                    if (ownx) gmax = fmax(gmax, sqrt(Rnd<T>::r(Rnd<T>::r(gxx * gxx) + Rnd<T>::r(gyx * gyx))));
+                    if (owny) gmax = fmax(gmax, sqrt(Rnd<T>::r(Rnd<T>::r(gxy * gxy) + Rnd<T>::r(gyy * gyy))));
+                }
+                Dm = Dc; Dc = Dn; v_m = v_c; v_c = v_n; v_n = v_nn; v_nn = v_n3; u_m = u_c; u_c = u_n; u_n = u_n2;
+                p_mm = p_m; p_m = p_c; mm = mc; mc = mn; mn = mn2;
+            }
+        }
+    }
+    if (ctl) {
+        block_atomic_max(dabs, &ctl->max_div_pre);
+        block_atomic_max(ch, &ctl->pois_change);
+        block_atomic_max(gmax, &ctl->max_grad);
+    }
+}
+
+void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
+                                 void* div_out, void* ua, void* va, double inv_dt, StepCtl* ctl, const uint8_t* flags,
+                                 int n_sm, cudaStream_t s) {
+    // chunks of 16..64 rows: two of a chunk's phi rows are recomputed by its neighbours
+    const int bx = (g.nx + FB_OWN - 1) / FB_OWN;
+    int rpb = 64;
+    while (rpb > 16 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
+    const int ntx = (g.nx + FT_W - 1) / FT_W;
+#define DCF(T, DIV) k_div_rb1_correct_fast<T, DIV><<<grid, FBT, 0, s>>>(g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)
+    if (dtype == 0) { if (div_out) DCF(double, true); else DCF(double, false); }
+    else { if (div_out) DCF(float, true); else DCF(float, false); }
+#undef DCF
+}
+
 }  // namespace b200cfd

@@ -50,6 +50,8 @@ ALGO_BYTES = {
     "poisson_correct": 16 + 8 + 8 + 16,  # K2 + K3 fused (default): R u*,v*  W phi, div_u_star, u, v
     "clean_sweep_1": 16 + 8,             # R u,v  W psi (psi_old = 0)
     "clean_apply_1": 24 + 16,            # R psi,u,v  W u,v
+    "clean_sweep_apply_1": 16 + 24,      # sweep + correction fused (default): R u,v  W psi,u,v (psi_old = 0)
+    "clean_sweep_apply_2": 24 + 24,      # (clean_iters > 2 only)
     "clean_sweep_2": 16 + 8 + 8,         # R u,v,psi_old  W psi
     "clean_apply_2": 24 + 16,            # (general path only; the fast path applies it inside finalize)
     "finalize": 24 + 16,                 # R psi,u,v  W u,v (last correction fused); ibm, mask only in flagged tiles

@@ -32,6 +32,7 @@ struct b200cfd_handle {
     StepScalars* ring = nullptr;
     int ring_cap = 8192;
     void *ua = nullptr, *va = nullptr, *psi[2] = {nullptr, nullptr}, *tmp = nullptr;
+    void *ub = nullptr, *vb = nullptr;   // second velocity pair: output of the clean sweep with the correction fused in
     double* ke_part = nullptr;
     double* red = nullptr;            // this slab's reduction vector (RED_N doubles)
     unsigned long long* cnt_part = nullptr;
@@ -39,6 +40,7 @@ struct b200cfd_handle {
     int n_part_used = 0;              // blocks of the finalize kernel in use
     uint8_t* flags = nullptr;         // tile-flag map of ibm / mask (step_fast.cu)
     bool fast = false;                // row-marching fast kernels applicable (decided when the fields are bound)
+    bool fuse_apply = false;          // clean sweep writes the corrected velocity itself: parity-green but measured SLOWER on B200 (the sweep is issue-bound), off unless B200CFD_FUSE_APPLY is set
     bool fuse_k23 = true;             // K2 + K3 in one kernel on the fast path (B200CFD_NO_FUSE_K23 turns it off)
     // caller-owned (bound) device memory
     void *u = nullptr, *v = nullptr, *phi = nullptr, *us = nullptr, *vs = nullptr, *div = nullptr, *tau = nullptr, *nu_t = nullptr;
@@ -137,6 +139,8 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     CUC(cudaMalloc(&h->ring, sizeof(StepScalars) * h->ring_cap));
     CUC(cudaMemset(h->ring, 0, sizeof(StepScalars) * h->ring_cap));
     CUC(cudaMalloc(&h->ua, fb)); CUC(cudaMalloc(&h->va, fb));
+    CUC(cudaMalloc(&h->ub, fb)); CUC(cudaMalloc(&h->vb, fb));
+    CUC(cudaMemset(h->ub, 0, fb)); CUC(cudaMemset(h->vb, 0, fb));
     CUC(cudaMalloc(&h->psi[0], fb)); CUC(cudaMalloc(&h->psi[1], fb));
     CUC(cudaMemset(h->ua, 0, fb)); CUC(cudaMemset(h->va, 0, fb));
     CUC(cudaMemset(h->psi[0], 0, fb)); CUC(cudaMemset(h->psi[1], 0, fb));   // psi borders must be 0 and are never written
@@ -163,7 +167,7 @@ int b200cfd_destroy(b200cfd_handle* h) {
     if (h->begin_graph) cudaGraphExecDestroy(h->begin_graph);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->tb) poisson_tb_destroy(h->tb);
-    cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
+    cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->ub); cudaFree(h->vb); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
     cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part); cudaFree(h->red); cudaFree(h->flags);
     delete h;
     return B200CFD_OK;
@@ -183,6 +187,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
         const void* ptrs[] = {u, v, phi, u_star, v_star, div_u_star, tau_supg, h->ua, h->va, h->psi[0], h->psi[1]};
         h->fast = h->cfg.use_supg && !h->cfg.use_les && fast_path_ok(h->g, ptrs, 11) && !getenv("B200CFD_NO_FAST");
         h->fuse_k23 = !getenv("B200CFD_NO_FUSE_K23");
+        h->fuse_apply = getenv("B200CFD_FUSE_APPLY") != nullptr;
         CU(h, cudaSetDevice(h->device));
         launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
         CU(h, cudaDeviceSynchronize());
@@ -249,8 +254,9 @@ static int enqueue_step_poisson(b200cfd_handle* h, cudaStream_t s) {
 }
 
 static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& idx);
+// out_u / out_v (in-step fast path only): where the velocity that still needs the deferred last correction lives
 static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, int mode, cudaStream_t s, void** last_psi, bool in_step = false,
-                         bool defer_last_apply = false) {
+                         bool defer_last_apply = false, void** out_u = nullptr, void** out_v = nullptr) {
     const int dt = h->cfg.dtype;
     const size_t fb = (size_t)h->cfg.ny * h->cfg.nx * h->es;
     int nl = 0;
@@ -272,9 +278,20 @@ static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, in
             void* pn = h->psi[it & 1];
             const void* po = it == 0 ? nullptr : h->psi[(it - 1) & 1];
             int pi = 0;
-            launch_clean_sweep(dt, h->g, h->clean, u, v, po, pn, s);
+            const bool last_deferred = defer_last_apply && it == iterations - 1;
+            if (out_u && out_v && h->fuse_apply && !last_deferred) {
+                // sweep + correction in one kernel, written to the other velocity pair
+                void* uo = (u == h->ua) ? h->ub : h->ua;
+                void* vo = (v == h->va) ? h->vb : h->va;
+                launch_clean_sweep(dt, h->g, h->clean, u, v, po, pn, uo, vo, s);
+                if (in_step) prof_mark(h, it == 0 ? "clean_sweep_apply_1" : "clean_sweep_apply_2", s, pi);
+                u = uo; v = vo;
+                ++nl; last = pn;
+                continue;
+            }
+            launch_clean_sweep(dt, h->g, h->clean, u, v, po, pn, nullptr, nullptr, s);
             if (in_step) prof_mark(h, it == 0 ? "clean_sweep_1" : "clean_sweep_2", s, pi);
-            if (!(defer_last_apply && it == iterations - 1)) {
+            if (!last_deferred) {
                 launch_clean_apply(dt, h->g, u, v, pn, s); ++nl;
                 if (in_step) prof_mark(h, it == 0 ? "clean_apply_1" : "clean_apply_2", s, pi);
             }
@@ -283,6 +300,8 @@ static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, in
         }
     }
     if (last_psi) *last_psi = last;
+    if (out_u) *out_u = u;
+    if (out_v) *out_v = v;
     return nl;
 }
 
@@ -298,7 +317,7 @@ static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& 
 static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     const b200cfd_config& c = h->cfg;
     const int dt = c.dtype;
-    int nl = 0, pi = 0;
+    int nl = 0, pi = 0, close_rb1 = 0;
     const void* nut = nullptr;
     prof_mark(h, nullptr, s, pi);
     if (c.use_les) { launch_smagorinsky(dt, h->g, h->u, h->v, h->nu_t, c.cs, s); nut = h->nu_t; ++nl; }
@@ -310,8 +329,8 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
         // K2 + K3 in one pass: u*, v* are read once and phi is never re-read
         launch_div_rb1_correct_fast(dt, h->g, h->us, h->vs, h->mask, h->phi, h->div, h->ua, h->va, h->phys.inv_cfg_dt, h->ctl,
                                     h->flags, h->n_sm, s);
-        launch_rb1_close(h->ctl, c.pressure_tolerance, s);
-        nl += 2;
+        close_rb1 = 1;               // the Poisson bookkeeping of k_rb1_close is folded into the end-of-step control kernel
+        nl += 1;
         prof_mark(h, "poisson_correct", s, pi);
     } else {
         nl += enqueue_step_poisson(h, s);
@@ -322,14 +341,16 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     // fast path: the last clean-divergence correction u,v -= grad(psi) is applied on the fly by the finalize kernel
     const bool defer = h->fast && c.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && c.clean_iters > 0;
     void* last_psi = nullptr;
-    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer);
+    void *fu = h->ua, *fv = h->va;   // velocity entering the finalize kernel
+    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer, defer ? &fu : nullptr, defer ? &fv : nullptr);
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
-    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, h->ua, h->va, defer ? last_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
+    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
     else launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s);
     ++nl;
     prof_mark(h, "finalize", s, pi);
-    launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, s); ++nl;
-    if (close) { launch_ctl_end_step(h->ctl, h->cp, h->red, 1, h->ring, h->ring_cap, s); ++nl; }
+    if (close) launch_ctl_reduce_end(h->ctl, h->cp, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->ring, h->ring_cap, s);
+    else launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, s);
+    ++nl;
     prof_mark(h, "ctl", s, pi);
     if (h->profiling) ++h->prof_steps;
     return nl;

@@ -72,10 +72,15 @@ template <int VEC> struct Row4<float, VEC> {
     }
 };
 
-template <typename T, bool HAS_OLD, int VEC>
+// APPLY: the correction u,v -= grad(psi_new) (v5.py:254-256) of the SAME iteration is fused in as a lagged epilogue: once
+// row i of psi_new exists, row i-1 of the corrected velocity (psi rows i-2, i-1, i; x-neighbours by shuffle) is written
+// to uo, vo (separate buffers: neighbouring tiles still read u, v in their aprons).  The tile then marches one row past
+// its owned rows; the first / last strip also carry the local border columns and the first / last tile the wall rows
+// (copied unchanged), so uo, vo are complete fields.  Saves the 40 B/cell pass of k_clean_apply minus 16 B/cell.
+template <typename T, bool HAS_OLD, int VEC, bool APPLY>
 __global__ void __launch_bounds__(32 * CWARPS)
 k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ pold,
-              T* __restrict__ pnew) {
+              T* __restrict__ pnew, T* __restrict__ uo, T* __restrict__ vo) {
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * CWARPS + (threadIdx.x >> 5);
     if (tile >= cp.n_strips * cp.n_tiles) return;          // whole warp exits together
@@ -103,6 +108,23 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
 
     double xprev[CPL], v_im1[CPL], v_i[CPL], pcur[CPL];
     double ucur[CPL], vnext[CPL], pnext[CPL];
+    double xprev2[CPL] = {0.0, 0.0, 0.0, 0.0}, uprev[CPL] = {0.0, 0.0, 0.0, 0.0};   // APPLY: psi row i-2, u row i-1
+    // APPLY: columns this warp writes uo, vo for = owned columns + the local border column of the first / last strip
+    const int jsA = (s == 0) ? 0 : js, jeA = (s == cp.n_strips - 1) ? nx : je;
+    if (APPLY) {
+        if (t == 0 || t == cp.n_tiles - 1) {                  // wall rows: copied unchanged
+            const long long rw = (t == 0) ? 0 : (long long)(g.ny - 1) * g.pitch;
+#pragma unroll
+            for (int m = 0; m < CPL; ++m) {
+                const int c = c0 + m;
+                if (c >= jsA && c < jeA) {
+                    uo[rw + c] = u[rw + c]; vo[rw + c] = v[rw + c];
+                    if (cp.n_tiles == 1) { const long long r2 = (long long)(g.ny - 1) * g.pitch; uo[r2 + c] = u[r2 + c]; vo[r2 + c] = v[r2 + c]; }
+                }
+            }
+        }
+    }
+    const int iend = APPLY ? ie : ie - 1;                      // last row marched (APPLY: one past the owned rows)
     {
         const long long rm = (long long)(iw0 - 1) * g.pitch, r0 = (long long)iw0 * g.pitch;
         typedef Row4<T, VEC> R4;
@@ -123,13 +145,13 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         }
     }
 
-    for (int i = iw0; i < ie; ++i) {
+    for (int i = iw0; i <= iend; ++i) {
         // ---- issue next row's loads (row i+1: u row i+1, v row i+2, psi_old row i+2) and an L2 prefetch ahead
         double un_[CPL], vn2[CPL], pn2[CPL];
         {
-            const bool more = (i + 1 < ie);
+            const bool more = (i + 1 <= iend) && (i + 1 < g.ny - 1);
             const long long r1 = (long long)(i + 1) * g.pitch, r2 = r1 + g.pitch;
-            if (more) {                                            // row i+2 <= ny-1 because i+1 < ie <= ny-1
+            if (more) {                                            // row i+2 <= ny-1 because i+1 <= ny-2
                 Row4<T, VEC>::ld(u, r1, c0, nx, un_);
                 Row4<T, VEC>::ld(v, r2, c0, nx, vn2);
                 if (HAS_OLD) Row4<T, VEC>::ld(pold, r2, c0, nx, pn2);
@@ -140,13 +162,15 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
                 if (!(HAS_OLD && more)) pn2[m] = 0.0;
             }
             const int ip = i + CPFD;
-            if (ip < ie && c0 >= 0 && c0 < nx) {
+            if (ip < ie && c0 >= 0 && c0 < nx) {   // (APPLY marches to ie: that row is prefetched by the tile that owns it)
                 const long long rp = (long long)ip * g.pitch + c0;
                 prefetch_l2(u + rp);
                 prefetch_l2(v + rp + g.pitch);
                 if (HAS_OLD) prefetch_l2(pold + rp + g.pitch);
             }
         }
+        double x[CPL] = {0.0, 0.0, 0.0, 0.0};
+        if (!APPLY || i < g.ny - 1) {                              // (APPLY: row ny-1 is the wall, psi = 0 there)
         // ---- right-hand side of row i
         const double uE3 = __shfl_down_sync(0xffffffffu, ucur[0], 1);
         const double uW0 = __shfl_up_sync(0xffffffffu, ucur[CPL - 1], 1);
@@ -174,7 +198,6 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         tmp = __shfl_up_sync(0xffffffffu, B, 16); if (lane >= 16) B = fma(a64, tmp, B);
         double carry = __shfl_up_sync(0xffffffffu, B, 1);
         if (lane == 0) carry = 0.0;
-        double x[CPL];
         x[0] = Rnd<T>::r(fma(alpha, carry, t0));
         x[1] = Rnd<T>::r(fma(a2, carry, t1));
         x[2] = Rnd<T>::r(fma(a3, carry, t2));
@@ -182,8 +205,9 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         // a non-updated column keeps psi = 0 but the scan leaks alpha^k x into it: force it
 #pragma unroll
         for (int m = 0; m < CPL; ++m) if (!colin[m]) x[m] = 0.0;
+        }
         // ---- store owned cells
-        if (i >= is) {
+        if (i >= is && i < ie) {
             const long long ro = (long long)i * g.pitch;
             if (VEC && c0 >= js && c0 + CPL <= je) {
                 Row4<T, VEC>::st(pnew, ro + c0, x);
@@ -195,9 +219,31 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
                 }
             }
         }
+        // ---- APPLY: corrected velocity of row i-1 from psi rows i-2 (xprev2), i-1 (xprev), i (x)
+        if (APPLY && i - 1 >= is) {
+            const double xE3 = __shfl_down_sync(0xffffffffu, xprev[0], 1);
+            const double xW0 = __shfl_up_sync(0xffffffffu, xprev[CPL - 1], 1);
+            const long long ro = (long long)(i - 1) * g.pitch;
+#pragma unroll
+            for (int m = 0; m < CPL; ++m) {
+                const int c = c0 + m;
+                double gx = 0.0, gy = 0.0;
+                if (colin[m]) {
+                    const double xE = (m < CPL - 1) ? xprev[(m + 1) % CPL] : xE3;
+                    const double xW = (m > 0) ? xprev[(m + CPL - 1) % CPL] : xW0;
+                    gx = Rnd<T>::r((xE - xW) * g.hdx);
+                    gy = Rnd<T>::r((x[m] - xprev2[m]) * g.hdy);
+                }
+                if (c >= jsA && c < jeA) {
+                    uo[ro + c] = (T)(uprev[m] - gx);
+                    vo[ro + c] = (T)(v_im1[m] - gy);
+                }
+            }
+        }
         // ---- rotate
 #pragma unroll
         for (int m = 0; m < CPL; ++m) {
+            xprev2[m] = xprev[m]; uprev[m] = ucur[m];
             xprev[m] = x[m];
             v_im1[m] = v_i[m]; v_i[m] = vnext[m]; vnext[m] = vn2[m];
             pcur[m] = pnext[m]; pnext[m] = pn2[m];
@@ -264,32 +310,38 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
 
 template <typename T>
 static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void* u, const void* v, const void* psi_old,
-                                 void* psi_new, int nblk, cudaStream_t s) {
+                                 void* psi_new, void* uo, void* vo, int nblk, cudaStream_t s) {
     // vector path: the window origin 1 + s*strip_w - apron_h is a multiple of 4 by construction (clean_plan)
     const size_t al = 4 * sizeof(T);
     const bool vec = g.pitch % 4 == 0 && (cp.j_first - cp.apron_h) % 4 == 0 && cp.strip_w % 4 == 0 &&
                      ((size_t)u % al) == 0 && ((size_t)v % al) == 0 && ((size_t)psi_old % al) == 0 && ((size_t)psi_new % al) == 0;
     const T *up = (const T*)u, *vp = (const T*)v, *po = (const T*)psi_old;
-    T* pn = (T*)psi_new;
+    T *pn = (T*)psi_new, *uop = (T*)uo, *vop = (T*)vo;
+    // measured on B200: the scalar form is the fastest (the kernel is latency-, not L1-wavefront-bound); 1 / 2 kept as knobs
     const int mode = vec ? tune_int("B200CFD_CLEAN_VEC", 0) : 0;
-#define SWEEP_LAUNCH(V)                                                                                   \
-    do {                                                                                                  \
-        if (po) k_clean_sweep<T, true, V><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, po, pn);            \
-        else k_clean_sweep<T, false, V><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, nullptr, pn);         \
+#define SWEEP_LAUNCH(V, A)                                                                                          \
+    do {                                                                                                            \
+        if (po) k_clean_sweep<T, true, V, A><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, po, pn, uop, vop);         \
+        else k_clean_sweep<T, false, V, A><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, nullptr, pn, uop, vop);      \
     } while (0)
-    if (mode == 1) SWEEP_LAUNCH(1);
-    else if (mode == 2) SWEEP_LAUNCH(2);
-    else SWEEP_LAUNCH(0);
+    if (uo && vo) {
+        SWEEP_LAUNCH(0, true);
+    } else {
+        if (mode == 1) SWEEP_LAUNCH(1, false);
+        else if (mode == 2) SWEEP_LAUNCH(2, false);
+        else SWEEP_LAUNCH(0, false);
+    }
 #undef SWEEP_LAUNCH
 }
 
+// uo, vo != NULL: also write the corrected velocity u,v - grad(psi_new) there (complete fields, borders copied)
 void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
-                        const void* psi_old, void* psi_new, cudaStream_t s) {
+                        const void* psi_old, void* psi_new, void* uo, void* vo, cudaStream_t s) {
     const int ntile = cp.n_strips * cp.n_tiles;
     const int nblk = (ntile + CWARPS - 1) / CWARPS;
     if (nblk <= 0) return;
-    if (dtype == 0) launch_clean_sweep_t<double>(g, cp, u, v, psi_old, psi_new, nblk, s);
-    else launch_clean_sweep_t<float>(g, cp, u, v, psi_old, psi_new, nblk, s);
+    if (dtype == 0) launch_clean_sweep_t<double>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
+    else launch_clean_sweep_t<float>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
 }
 
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s) {

@@ -46,8 +46,12 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
                      double* ke_partials, unsigned long long* cnt_partials, cudaStream_t s);
 int finalize_num_partials(const Geom& g);
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s);
-void launch_ctl_reduce_local(const StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
-                             int n_partials, double* red, cudaStream_t s);
+void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
+                             int n_partials, double* red, int close_rb1, double tol, cudaStream_t s);
+// one GPU: reduce_local + end_step in one launch
+void launch_ctl_reduce_end(StepCtl* ctl, const CtlParams& cp, const double* ke_partials, const unsigned long long* cnt_partials,
+                           int n_partials, double* red, int close_rb1, double tol, StepScalars* ring, int ring_cap,
+                           cudaStream_t s);
 void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
                          int ring_cap, cudaStream_t s);
 // ---- x-slab halos: strided columns <-> contiguous buffer [ny][ncols] (halo.cu) -------------------
@@ -91,7 +95,8 @@ void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, co
 struct CleanPlan { int strip_w, tile_h, apron_h, apron_v; int n_strips, n_tiles; int j_first, j_end; };
 CleanPlan clean_plan(const Geom& g, int dtype, int n_sm);
 void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
-                        const void* psi_old /*NULL = zeros*/, void* psi_new, cudaStream_t s);
+                        const void* psi_old /*NULL = zeros*/, void* psi_new, void* uo /*NULL = no fused correction*/, void* vo,
+                        cudaStream_t s);
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s);
 
 }  // namespace b200cfd

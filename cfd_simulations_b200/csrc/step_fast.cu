@@ -11,6 +11,7 @@
 // Reference: python/flow_over_cylinder (Fischer)/v5.py:127-176 (SUPG, convection, Laplacian), :178-226 (divergence,
 // red-black iteration), :349-360 (BC), :228-237 (IBM), :421-438 (diagnostics, clip).
 #include "kernels.h"
+#include <cstdlib>
 #include "cellmath.cuh"
 
 namespace b200cfd {
@@ -488,8 +489,9 @@ void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* v
 
 static inline dim3 finalize_fast_grid(const Geom& g, int n_sm, int* rpb_out) {
     const int bx = (g.nx + FB_OWN - 1) / FB_OWN;
+    static const int rpb_min = getenv("B200CFD_FIN_RPB_MIN") ? atoi(getenv("B200CFD_FIN_RPB_MIN")) : 16;   // developer knob
     int rpb = 64;
-    while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    while (rpb > rpb_min && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
     *rpb_out = rpb;
     return dim3(bx, (g.ny + rpb - 1) / rpb);
 }

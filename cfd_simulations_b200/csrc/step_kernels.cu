@@ -273,8 +273,10 @@ __global__ void k_ctl_zero_max(StepCtl* c) { if (!threadIdx.x && !blockIdx.x) { 
 
 // End of a step, part 1: fold this slab's running maxima and the fixed-order sum of its energy partials into the
 // reduction vector red[RED_N] (what the slabs all_gather; on one GPU part 2 reads it directly).
-__global__ void k_ctl_reduce_local(const StepCtl* __restrict__ c, const double* __restrict__ ke_part,
-                                   const unsigned long long* __restrict__ cnt_part, int n_part, double* __restrict__ red) {
+// close_rb1: the "as executed" Poisson bookkeeping (what k_rb1_close does) is folded in here, saving a launch per step.
+__device__ __forceinline__ void ctl_reduce_local(StepCtl* c, const double* __restrict__ ke_part,
+                                                 const unsigned long long* __restrict__ cnt_part, int n_part,
+                                                 double* __restrict__ red, int close_rb1, double tol) {
     __shared__ double s_e[256];
     __shared__ unsigned long long s_c[256];
     double e = 0.0; unsigned long long n = 0;
@@ -286,6 +288,10 @@ __global__ void k_ctl_reduce_local(const StepCtl* __restrict__ c, const double* 
         __syncthreads();
     }
     if (threadIdx.x) return;
+    if (close_rb1) {
+        const double ch = bits_to_double(c->pois_change);
+        c->pois_last = ch; c->pois_iters = 1; c->pois_change = 0ull; c->pois_done = ch < tol ? 1 : 0;
+    }
     red[RED_MAX_DIV_PRE] = bits_to_double(c->max_div_pre);
     red[RED_MAX_GRAD] = bits_to_double(c->max_grad);
     red[RED_MAX_DIV_POST] = bits_to_double(c->max_div_post);
@@ -301,9 +307,8 @@ __global__ void k_ctl_reduce_local(const StepCtl* __restrict__ c, const double* 
 
 // End of a step, part 2: combine the reduction vectors of all slabs (max is exact and order independent; the energy sum
 // is taken in rank order), write the ring record, prepare the next step's dt / ramps (adaptive_time_step, v5.py:316-326).
-__global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ gathered, int nranks,
-                               StepScalars* ring, int cap) {
-    if (threadIdx.x || blockIdx.x) return;
+__device__ __forceinline__ void ctl_end_step(StepCtl* c, const CtlParams& cp, const double* gathered, int nranks,
+                                             StepScalars* ring, int cap) {
     double m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double es = 0.0, ec = 0.0;
     for (int r = 0; r < nranks; ++r) {
@@ -328,6 +333,23 @@ __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restric
     c->in_max_u = r.max_abs_u; c->in_max_v = r.max_abs_v;
     c->step += 1;
     ctl_prepare(c, cp);
+}
+__global__ void k_ctl_reduce_local(StepCtl* c, const double* __restrict__ ke_part, const unsigned long long* __restrict__ cnt_part,
+                                   int n_part, double* __restrict__ red, int close_rb1, double tol) {
+    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol);
+}
+__global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ gathered, int nranks,
+                               StepScalars* ring, int cap) {
+    if (threadIdx.x || blockIdx.x) return;
+    ctl_end_step(c, cp, gathered, nranks, ring, cap);
+}
+// one GPU: both parts in one launch (thread 0 wrote red itself, so it can read it back without a fence)
+__global__ void k_ctl_reduce_end(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
+                                 const unsigned long long* __restrict__ cnt_part, int n_part, double* red, int close_rb1,
+                                 double tol, StepScalars* ring, int cap) {
+    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol);
+    if (threadIdx.x) return;
+    ctl_end_step(c, cp, red, 1, ring, cap);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -407,9 +429,14 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s) {
     k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max);
 }
-void launch_ctl_reduce_local(const StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
-                             int n_partials, double* red, cudaStream_t s) {
-    k_ctl_reduce_local<<<1, 256, 0, s>>>(ctl, ke_partials, cnt_partials, n_partials, red);
+void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
+                             int n_partials, double* red, int close_rb1, double tol, cudaStream_t s) {
+    k_ctl_reduce_local<<<1, 256, 0, s>>>(ctl, ke_partials, cnt_partials, n_partials, red, close_rb1, tol);
+}
+void launch_ctl_reduce_end(StepCtl* ctl, const CtlParams& cp, const double* ke_partials, const unsigned long long* cnt_partials,
+                           int n_partials, double* red, int close_rb1, double tol, StepScalars* ring, int ring_cap,
+                           cudaStream_t s) {
+    k_ctl_reduce_end<<<1, 256, 0, s>>>(ctl, cp, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, ring, ring_cap);
 }
 void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
                          int ring_cap, cudaStream_t s) {

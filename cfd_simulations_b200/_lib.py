@@ -9,9 +9,10 @@ PKG = Path(__file__).resolve().parent
 LIB_PATH = PKG / "libb200cfd.so"
 
 F64, F32 = 0, 1
-POISSON_AS_EXECUTED, POISSON_AS_WRITTEN, POISSON_JACOBI = 0, 1, 2
+POISSON_AS_EXECUTED, POISSON_AS_WRITTEN, POISSON_JACOBI, POISSON_SOR_V2 = 0, 1, 2, 3
 CLEANDIV_LEXICOGRAPHIC, CLEANDIV_REDBLACK = 0, 1
-POISSON_MODES = {"as_executed": POISSON_AS_EXECUTED, "as_written": POISSON_AS_WRITTEN, "jacobi": POISSON_JACOBI}
+POISSON_MODES = {"as_executed": POISSON_AS_EXECUTED, "as_written": POISSON_AS_WRITTEN, "jacobi": POISSON_JACOBI,
+                 "sor_v2": POISSON_SOR_V2}
 CLEANDIV_MODES = {"lexicographic": CLEANDIV_LEXICOGRAPHIC, "redblack": CLEANDIV_REDBLACK}
 
 

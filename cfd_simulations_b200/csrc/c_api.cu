@@ -584,6 +584,31 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
             if (a != phi) CU(h, cudaMemcpyAsync(phi, a, fb, cudaMemcpyDeviceToDevice, s));
         }
         done_iters = max_iter;
+    } else if (mode == B200CFD_POISSON_SOR_V2) {
+        // v2.py:284-306: SOR on lap(phi) = +div/dt (sign flipped w.r.t. v5: inv_dt < 0), wall conditions after every
+        // sweep, stop when max|dphi| < tol.  Red-black ordering (north_star): same fixed point as the reference's
+        // lexicographic sweep, reached along a different path.
+        if (h->cfg.nranks > 1) return fail(h, B200CFD_EINVAL, "SOR_V2 is single-slab only");
+        const double inv_dt = -1.0 / dt;
+        const bool check = (tol > 0.0);
+        const int chunk = 32;
+        int it = 0;
+        while (it < max_iter) {
+            const int m = (max_iter - it < chunk) ? max_iter - it : chunk;
+            for (int q = 0; q < m; ++q) {
+                launch_rbgs_color(dtp, g, phi, rhs_div, mask, inv_dt, omega, 0, h->ctl, tol, 0, s);
+                launch_rbgs_color(dtp, g, phi, rhs_div, mask, inv_dt, omega, 1, h->ctl, tol, 1, s);
+                launch_sor_v2_bc(dtp, g, phi, h->ctl, s);
+            }
+            it += m;
+            if (check) {
+                int done = 0;
+                CU(h, cudaMemcpyAsync(&done, &h->ctl->pois_done, sizeof(int), cudaMemcpyDeviceToHost, s));
+                CU(h, cudaStreamSynchronize(s));
+                if (done) break;
+            }
+        }
+        done_iters = it;
     } else {
         const int iters = mode == B200CFD_POISSON_AS_EXECUTED ? (max_iter < 1 ? max_iter : 1) : max_iter;
         const double inv_dt = 1.0 / dt;

@@ -86,6 +86,8 @@ void launch_rbgs_color(int dtype, const Geom& g, void* phi, const void* div, con
                        double omega, int color, StepCtl* ctl, double tol, int close_iteration, cudaStream_t s);
 void launch_jacobi(int dtype, const Geom& g, const void* phi_in, void* phi_out, const void* div, const uint8_t* mask,
                    double dx2_over_dt, cudaStream_t s);
+// Neumann left/bottom/top, Dirichlet-0 right of v1/v2 solve_pressure_iterative (v2.py:299-303)
+void launch_sor_v2_bc(int dtype, const Geom& g, void* phi, const StepCtl* ctl, cudaStream_t s);
 void launch_poisson_reset(StepCtl* ctl, cudaStream_t s);
 // fused div(u*,v*) + exactly one red-black iteration from phi = 0 ("as executed"), + max|div|
 void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,

@@ -122,6 +122,32 @@ void launch_jacobi(int dtype, const Geom& g, const void* in, void* out, const vo
     else
         k_jacobi<float><<<pgrid(g), kPBlock, 0, s>>>(g, (const float*)in, (float*)out, (const float*)div, mask, dx2_over_dt);
 }
+// v2.py:299-303 (v1.py:290-294): after every SOR sweep  phi[:,0] = phi[:,1]; phi[:,-1] = 0; phi[0,:] = phi[1,:];
+// phi[-1,:] = phi[-2,:]  (in this order: the wall rows copy the already updated side columns, so the corners end as
+// phi[1,1], 0, phi[-2,1], 0).  One launch: the column part skips the wall rows, the row part reproduces the corners.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_sor_v2_bc(Geom g, T* __restrict__ phi, const StepCtl* __restrict__ ctl) {
+    (void)ctl;   // always applied: idempotent once the colour kernels have stopped, and the stopping sweep needs it
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    if (t >= 1 && t < g.ny - 1) {
+        const long long r = (long long)t * g.pitch;
+        phi[r] = phi[r + 1];
+        phi[r + g.nx - 1] = (T)0;
+    }
+    if (t < g.nx) {
+        const int jr = t == 0 ? 1 : t;                                  // column whose value the wall rows copy
+        const long long r1 = g.pitch, rm = (long long)(g.ny - 2) * g.pitch, rl = (long long)(g.ny - 1) * g.pitch;
+        const bool right = t == g.nx - 1;
+        phi[t] = right ? (T)0 : phi[r1 + jr];
+        phi[rl + t] = right ? (T)0 : phi[rm + jr];
+    }
+}
+void launch_sor_v2_bc(int dtype, const Geom& g, void* phi, const StepCtl* ctl, cudaStream_t s) {
+    const int n = g.nx > g.ny ? g.nx : g.ny;
+    if (dtype == 0) k_sor_v2_bc<double><<<(n + 255) / 256, 256, 0, s>>>(g, (double*)phi, ctl);
+    else k_sor_v2_bc<float><<<(n + 255) / 256, 256, 0, s>>>(g, (float*)phi, ctl);
+}
 void launch_poisson_reset(StepCtl* ctl, cudaStream_t s) { k_poisson_reset<<<1, 32, 0, s>>>(ctl); }
 
 void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,

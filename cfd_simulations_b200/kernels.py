@@ -196,3 +196,13 @@ def solve_pressure_jacobi(phi, div_u_star, dx, dt, mask, sweeps, temporal_depth=
     if not isinstance(phi, torch.Tensor):
         phi[...] = dp.cpu().numpy()
     return phi
+
+
+def solve_pressure_iterative(div_u_star, dx, dy, dt, mask, max_iter=500, tol=1e-7, omega=1.5, return_info=False):
+    """v2.py:284-306 (v1.py:275-297) solve_pressure_iterative: the SOR fallback of the v1/v2 solvers on
+    lap(phi) = +div/dt, Neumann left/bottom/top, Dirichlet-0 right, masked cells 0, phi starts at 0, stop when
+    max|dphi| < tol (<= max_iter sweeps).  Red-black ordering on the GPU: same converged field as the reference's
+    lexicographic sweep."""
+    return solve_pressure_gauss_seidel_fast(np.zeros_like(div_u_star) if not isinstance(div_u_star, torch.Tensor)
+                                            else torch.zeros_like(div_u_star), div_u_star, dx, dy, dt, mask, max_iter, tol,
+                                            omega=omega, mode="sor_v2", temporal_depth=1, return_info=return_info)

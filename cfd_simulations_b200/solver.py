@@ -305,6 +305,13 @@ class OptimizedTurbulentSolver:
         out = t if isinstance(div_u_star, torch.Tensor) else t.cpu().numpy()
         return (out, it.value, last.value) if return_info else out
 
+    def solve_pressure_iterative(self, div_u_star, max_iter=500, tol=1e-7, omega=1.5, return_info=False):
+        """v2.py:284-306 (RobustTurbulentSolver.solve_pressure_iterative; v1.py:275-297 with 200 / 1e-6): the SOR fallback
+        of the v1/v2 solvers on lap(phi) = +div/dt with Neumann left/bottom/top and Dirichlet-0 right walls, masked cells 0.
+        Red-black ordering on the GPU: converges to the same field as the reference's lexicographic sweep."""
+        return self.solve_pressure_fast(div_u_star, mode="sor_v2", max_iter=max_iter, tol=tol, omega=omega, temporal_depth=1,
+                                        return_info=return_info)
+
     def apply_boundary_conditions(self, u, v):
         """v5.py:349-360, in place on numpy arrays or CUDA tensors, at the solver's current step."""
         from . import kernels

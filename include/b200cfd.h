@@ -34,7 +34,11 @@ enum { B200CFD_OK = 0, B200CFD_EINVAL = -1, B200CFD_ECUDA = -2, B200CFD_ENOMEM =
 enum {
     B200CFD_POISSON_AS_EXECUTED = 0, /* v5.py:202-226 under Numba parallel=True: exactly 1 red-black iteration */
     B200CFD_POISSON_AS_WRITTEN  = 1, /* same source, true max|dphi| reduction, tolerance break, <= N iterations */
-    B200CFD_POISSON_JACOBI      = 2  /* v5.py:336-346 (use_fast_pressure=False): fixed sweep count, 0.25 / dx^2 */
+    B200CFD_POISSON_JACOBI      = 2, /* v5.py:336-346 (use_fast_pressure=False): fixed sweep count, 0.25 / dx^2 */
+    B200CFD_POISSON_SOR_V2      = 3  /* v2.py:284-306 / v1.py:275-297 solve_pressure_iterative: SOR on lap(phi) = +div/dt,
+                                        Neumann left/bottom/top, Dirichlet-0 right after every sweep, max|dphi| < tol stop;
+                                        red-black ordering (same converged field as the reference's lexicographic sweep);
+                                        b200cfd_poisson only, not a time-step mode */
 };
 enum {
     B200CFD_CLEANDIV_LEXICOGRAPHIC = 0, /* v5.py:250-253 at one Numba thread: lexicographic Gauss-Seidel (parity mode) */
@@ -141,7 +145,8 @@ int b200cfd_fetch_scalars(b200cfd_handle* h, int64_t first_step, int n, b200cfd_
 /* solve_pressure_fast / solve_pressure_gauss_seidel_fast (v5.py:328-347, 202-226) on arbitrary
  * device arrays: phi (in/out, NOT zeroed here), rhs_div = div_u_star, mask may be NULL.
  * mode: AS_EXECUTED (1 iteration), AS_WRITTEN (<= max_iter, tolerance break, exact per-iteration max),
- * JACOBI (max_iter sweeps; uses dx only).  omega = 1 is the reference; omega != 1 is red-black SOR.
+ * JACOBI (max_iter sweeps; uses dx only), SOR_V2 (v1/v2 fallback solver, omega = 1.5 there).  omega = 1 is the v5
+ * reference; omega != 1 is red-black SOR.
  * temporal_depth T >= 1: iterations fused per HBM pass by the shared-memory (TMA) kernel; 0 = auto.
  * iters_done / last_change (host pointers, may be NULL) are written after a stream sync when non-NULL. */
 int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uint8_t* mask,

@@ -72,7 +72,7 @@ EXPORTS = [
     "b200cfd_bind_fields", "b200cfd_set_step", "b200cfd_get_step", "b200cfd_step", "b200cfd_step_host",
     "b200cfd_launches_per_step", "b200cfd_health", "b200cfd_profile_begin", "b200cfd_profile_end", "b200cfd_get_clean_plan", "b200cfd_fetch_scalars", "b200cfd_poisson",
     "b200cfd_k_supg_tau", "b200cfd_k_convection", "b200cfd_k_laplacian", "b200cfd_k_divergence",
-    "b200cfd_k_gradient", "b200cfd_k_smagorinsky", "b200cfd_k_apply_bc", "b200cfd_k_apply_ibm",
+    "b200cfd_k_gradient", "b200cfd_k_smagorinsky", "b200cfd_k_vorticity", "b200cfd_k_apply_bc", "b200cfd_k_apply_ibm",
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
     "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len",
     "b200cfd_set_step_global", "b200cfd_pack_columns", "b200cfd_unpack_columns",
@@ -115,6 +115,7 @@ def load():
     lib.b200cfd_k_divergence.argtypes = [vp, vp, vp, vp, vp]
     lib.b200cfd_k_gradient.argtypes = [vp, vp, vp, vp, vp]
     lib.b200cfd_k_smagorinsky.argtypes = [vp, vp, vp, vp, dbl, vp]
+    lib.b200cfd_k_vorticity.argtypes = [vp, vp, vp, vp, vp, vp]
     lib.b200cfd_k_apply_bc.argtypes = [vp, vp, vp, vp, i64, vp]
     lib.b200cfd_k_apply_ibm.argtypes = [vp, vp, vp, vp, dbl, vp]
     lib.b200cfd_k_clean_divergence.argtypes = [vp, vp, vp, i32, i32, vp, vp]

@@ -683,6 +683,9 @@ int b200cfd_k_gradient(b200cfd_handle* h, const void* phi, void* gx, void* gy, v
 int b200cfd_k_smagorinsky(b200cfd_handle* h, const void* u, const void* v, void* nu_t, double cs, void* stream) {
     UNIT_PRE(); launch_smagorinsky(h->cfg.dtype, h->g, u, v, nu_t, cs, s); UNIT_POST();
 }
+int b200cfd_k_vorticity(b200cfd_handle* h, const void* u, const void* v, const uint8_t* mask, void* w, void* stream) {
+    UNIT_PRE(); launch_vorticity(h->cfg.dtype, h->g, u, v, mask, w, s); UNIT_POST();
+}
 int b200cfd_k_apply_bc(b200cfd_handle* h, void* u, void* v, const double* y, int64_t step, void* stream) {
     UNIT_PRE(); launch_apply_bc(h->cfg.dtype, h->g, u, v, y, h->cfg.V_inf, h->cfg.y_max, (long long)step, s); UNIT_POST();
 }

@@ -45,6 +45,8 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
                      void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
                      double* ke_partials, unsigned long long* cnt_partials, cudaStream_t s);
 int finalize_num_partials(const Geom& g);
+// compute_vorticity (v5.py:365-373), for the snapshot writer
+void launch_vorticity(int dtype, const Geom& g, const void* u, const void* v, const uint8_t* mask, void* w, cudaStream_t s);
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s);
 void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
                              int n_partials, double* red, int close_rb1, double tol, cudaStream_t s);

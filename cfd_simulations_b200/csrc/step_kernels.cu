@@ -426,6 +426,26 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
              (k_finalize<double><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const double*)ua, (const double*)va, (double*)u, (double*)v, ibm, mask, y, ke_partials, cnt_partials)),
              (k_finalize<float><<<grid2d(g), kBlock, 0, s>>>(g, p, ctl, (const float*)ua, (const float*)va, (float*)u, (float*)v, ibm, mask, y, ke_partials, cnt_partials)));
 }
+// compute_vorticity (v5.py:365-373): central differences on the interior, 0 on the border, NaN inside the cylinder;
+// arithmetic in the field dtype (NumPy keeps float32 arrays float32 against Python scalars)
+template <typename T>
+__global__ void __launch_bounds__(BX* BY)
+k_vorticity(Geom g, const T* __restrict__ u, const T* __restrict__ v, const uint8_t* __restrict__ mask, T* __restrict__ w) {
+    const int j = blockIdx.x * BX + threadIdx.x, i = blockIdx.y * BY + threadIdx.y;
+    if (i >= g.ny || j >= g.nx) return;
+    const long long k = i * g.pitch + j;
+    double o = 0.0;
+    if (is_interior(g, i, j))
+        o = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(ld(v, k + 1) - ld(v, k - 1)) / Rnd<T>::r(g.two_dx)) -
+                      Rnd<T>::r(Rnd<T>::r(ld(u, k + g.pitch) - ld(u, k - g.pitch)) / Rnd<T>::r(g.two_dy)));
+    if (mask && mask[k]) o = __longlong_as_double(0x7ff8000000000000ll);
+    w[k] = (T)o;
+}
+void launch_vorticity(int dtype, const Geom& g, const void* u, const void* v, const uint8_t* mask, void* w, cudaStream_t s) {
+    DISPATCH(dtype,
+             (k_vorticity<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, mask, (double*)w)),
+             (k_vorticity<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, mask, (float*)w)));
+}
 void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s) {
     k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max);
 }

@@ -330,6 +330,14 @@ class OptimizedTurbulentSolver:
         w[self.cylinder_mask] = np.nan
         return w
 
+    def compute_vorticity_device(self, out=None):
+        """compute_vorticity (v5.py:365-373) on the device: a CUDA tensor (NaN inside the cylinder), nothing crosses PCIe."""
+        u, v = self._d["u"], self._d["v"]
+        w = torch.empty_like(u) if out is None else out
+        check(self._lib.b200cfd_k_vorticity(self._h, u.data_ptr(), v.data_ptr(), self._d["mask"].data_ptr(), w.data_ptr(),
+                                            _stream_ptr(self.device)), self._h)
+        return w
+
     def _local_health(self):
         out = (C.c_double * 4)()
         check(self._lib.b200cfd_health(self._h, C.byref(out), _stream_ptr(self.device)), self._h)

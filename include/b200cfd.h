@@ -167,6 +167,9 @@ int b200cfd_k_divergence(b200cfd_handle* h, const void* u, const void* v, void* 
 int b200cfd_k_gradient(b200cfd_handle* h, const void* phi, void* gx, void* gy, void* stream);
 /* compute_smagorinsky_viscosity_fast (v5.py:96-110) */
 int b200cfd_k_smagorinsky(b200cfd_handle* h, const void* u, const void* v, void* nu_t, double cs, void* stream);
+/* OptimizedTurbulentSolver.compute_vorticity (v5.py:365-373): 0 on the border, NaN where mask != 0 (mask may be NULL);
+ * used by the snapshot writer (v5.py:454-470) so that only finished fields cross PCIe */
+int b200cfd_k_vorticity(b200cfd_handle* h, const void* u, const void* v, const uint8_t* mask, void* w, void* stream);
 /* apply_boundary_conditions (v5.py:349-360) for an explicit step index */
 int b200cfd_k_apply_bc(b200cfd_handle* h, void* u, void* v, const double* y, int64_t step, void* stream);
 /* apply_ibm_fast (v5.py:228-237) */

@@ -1,0 +1,86 @@
+"""GPU: the chunked driver (device-resident advance + asynchronous snapshots) against the reference's step-by-step loop
+(v5.py:642-670) on the same CUDA solver, and the device vorticity against compute_vorticity (v5.py:365-373)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(tmp_path, f32=False, **kw):
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    return OptimizedTurbulentConfig(nx=150, ny=46, memory_efficient=f32, output_dir=str(tmp_path / "out"),
+                                    hdf5_file="run.h5", save_interval=20, **kw)
+
+
+class _StepwiseView:
+    """Hides advance()/scalars so run_simulation falls back to one time_step() call per step, like main()."""
+
+    def __init__(self, s):
+        self._s = s
+        self.config = s.config
+
+    def time_step(self):
+        return self._s.time_step()
+
+    def health(self):
+        return self._s.health()
+
+    u = property(lambda self: self._s.u)
+    v = property(lambda self: self._s.v)
+    X = property(lambda self: self._s.X)
+    Y = property(lambda self: self._s.Y)
+
+    def compute_vorticity(self):
+        return self._s.compute_vorticity()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_device_vorticity_matches_reference_expression(tmp_path, f32):
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    s = OptimizedTurbulentSolver(_cfg(tmp_path, f32))
+    s.advance(7)
+    w = s.compute_vorticity_device().cpu().numpy()
+    ref = s.compute_vorticity()
+    assert np.array_equal(np.isnan(w), np.isnan(ref)) and np.isnan(w).any()
+    ok = ~np.isnan(ref)
+    assert np.abs(w[ok] - ref[ok]).max() <= (1e-12 if not f32 else 1e-5) * np.abs(ref[ok]).max()
+    s.close()
+
+
+def test_chunked_driver_equals_stepwise_loop(tmp_path):
+    from cfd_simulations_b200.driver import run_simulation
+    from cfd_simulations_b200.snapshot import SnapshotWriter, list_steps, load_snapshot
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    a = OptimizedTurbulentSolver(_cfg(tmp_path / "a"))
+    b = OptimizedTurbulentSolver(_cfg(tmp_path / "b"))
+    with SnapshotWriter(a.config, backend="npz") as wa:
+        ra = run_simulation(a, writer=wa, max_steps=45)
+    with SnapshotWriter(b.config, backend="npz") as wb:
+        rb = run_simulation(_StepwiseView(b), writer=wb, max_steps=45)
+    assert ra.steps == rb.steps == 45 and ra.saved_steps == rb.saved_steps == [0, 20, 40]
+    assert ra.dts == rb.dts and ra.current_time == rb.current_time
+    pa, pb = tmp_path / "a" / "out" / "run.h5", tmp_path / "b" / "out" / "run.h5"
+    assert list_steps(pa) == list_steps(pb) == [0, 20, 40]
+    for st in (0, 20, 40):
+        sa, sb = load_snapshot(pa, st), load_snapshot(pb, st)
+        # the asynchronous copy captured the state of step `st`, not a later one
+        assert np.array_equal(sa["u"], sb["u"]) and np.array_equal(sa["v"], sb["v"]) and sa["time"] == sb["time"]
+        ok = ~np.isnan(sb["vorticity"])
+        assert np.array_equal(np.isnan(sa["vorticity"]), ~ok)
+        assert np.abs(sa["vorticity"][ok] - sb["vorticity"][ok]).max() <= 1e-12 * np.abs(sb["vorticity"][ok]).max()
+    assert np.array_equal(a.u, b.u)
+    a.close(); b.close()
+
+
+def test_chunked_driver_stops_on_the_reference_step(tmp_path):
+    from cfd_simulations_b200.driver import run_simulation
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    T = 100.5 * float(np.float32(2e-5))
+    a = OptimizedTurbulentSolver(_cfg(tmp_path))
+    b = OptimizedTurbulentSolver(_cfg(tmp_path))
+    ra = run_simulation(a, T_total=T)
+    rb = run_simulation(_StepwiseView(b), T_total=T)
+    assert ra.steps == rb.steps and ra.current_time == rb.current_time >= T
+    assert abs(ra.steps - 101) <= 1           # float32 clock (NumPy 2 promotion of `current_time += dt`)
+    assert np.array_equal(a.u, b.u)
+    a.close(); b.close()

@@ -21,6 +21,13 @@ namespace b200cfd {
 #define FBT 128      // threads per block of the marching kernels
 #define FCOLS 256    // columns per block (2 per thread)
 
+// optional unrolling of the row loops (would remove the register-rotation moves; see the measurement below)
+#ifndef B200CFD_MARCH_UNROLL
+#define B200CFD_MARCH_UNROLL 1   // measured on B200: 3 spills (40 B stack) and is slower; 1 = no unrolling
+#endif
+#define MARCH_PRAGMA(x) _Pragma(#x)
+#define MARCH_UNROLL_N(n) MARCH_PRAGMA(unroll n)
+#define MARCH_UNROLL MARCH_UNROLL_N(B200CFD_MARCH_UNROLL)
 #define FPF 6        // L2 prefetch distance of the marching kernels, rows
 
 __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -144,6 +151,7 @@ k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __res
     D2 um = ld2<T>(u, k - g.pitch), uc = ld2<T>(u, k), vm = ld2<T>(v, k - g.pitch), vc = ld2<T>(v, k);
     D2 un = ld2<T>(u, k + g.pitch), vn = ld2<T>(v, k + g.pitch);
     double uw = hw ? ld(u, k - 1) : 0.0, ue = he ? ld(u, k + 2) : 0.0, vw = hw ? ld(v, k - 1) : 0.0, ve = he ? ld(v, k + 2) : 0.0;
+    MARCH_UNROLL
     for (int i = lo; i < hi; ++i, k += g.pitch) {
         // software pipeline: the loads of the NEXT iteration (row i+2, and the x-neighbours of row i+1) are issued now
         D2 un2 = {0, 0}, vn2 = {0, 0};
@@ -412,6 +420,7 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
             D2 urn = ld2g<T>(ua, ro + g.pitch, c0, inb), vrn = ld2g<T>(va, ro + g.pitch, c0, inb);
             if (PSI) pn = (lo + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
             D2 mn = (lo + 1 < g.ny - 1) ? mult_row(ro + g.pitch) : D2{1.0, 1.0};
+            MARCH_UNROLL
             for (int i = lo; i < hi; ++i, ro += g.pitch) {
                 // issue the loads of the NEXT iteration: stored row i+2, psi row i+3, ibm row i+2
                 D2 urn2 = {0, 0}, vrn2 = {0, 0}, pn2 = {0, 0}, mn2 = {1.0, 1.0};
@@ -612,6 +621,7 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
             // software pipeline: the rows the NEXT iteration consumes are requested one iteration ahead
             D2 v_nn = vrow(i + 2), u_n = urow(i + 1);
             uchar2 mn = mrow(i + 1);
+            MARCH_UNROLL
             for (; i <= hi; ++i) {
                 const long long k = (long long)i * g.pitch + c0;
                 if (inb && i + FPF < g.ny) { pf_l2(us + k + FPF * g.pitch); pf_l2(vs + k + FPF * g.pitch); }

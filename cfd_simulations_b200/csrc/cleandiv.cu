@@ -81,6 +81,7 @@ template <typename T, bool HAS_OLD, int VEC, bool APPLY>
 __global__ void __launch_bounds__(32 * CWARPS)
 k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ pold,
               T* __restrict__ pnew, T* __restrict__ uo, T* __restrict__ vo) {
+    pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * CWARPS + (threadIdx.x >> 5);
     if (tile >= cp.n_strips * cp.n_tiles) return;          // whole warp exits together
@@ -256,6 +257,7 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_clean_apply(Geom g, T* __restrict__ u, T* __restrict__ v, const T* __restrict__ psi) {
+    pdl_wait(); pdl_trigger();
     const int j = blockIdx.x * 64 + threadIdx.x, i = blockIdx.y * 4 + threadIdx.y;
     if (i < 1 || i >= g.ny - 1 || j < 1 || j >= g.nx - 1) return;
     const int jg = g.jg0 + j;
@@ -326,8 +328,8 @@ static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void*
     const int mode = vec ? tune_int("B200CFD_CLEAN_VEC", 0) : 0;
 #define SWEEP_LAUNCH(V, A)                                                                                          \
     do {                                                                                                            \
-        if (po) k_clean_sweep<T, true, V, A><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, po, pn, uop, vop);         \
-        else k_clean_sweep<T, false, V, A><<<nblk, 32 * CWARPS, 0, s>>>(g, cp, up, vp, nullptr, pn, uop, vop);      \
+        if (po) launch_pdl(k_clean_sweep<T, true, V, A>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, po, pn, uop, vop);         \
+        else launch_pdl(k_clean_sweep<T, false, V, A>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn, uop, vop);      \
     } while (0)
     if (uo && vo) {
         SWEEP_LAUNCH(0, true);
@@ -351,8 +353,8 @@ void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const voi
 
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s) {
     dim3 grid((g.nx + 63) / 64, (g.ny + 3) / 4), block(64, 4);
-    if (dtype == 0) k_clean_apply<double><<<grid, block, 0, s>>>(g, (double*)u, (double*)v, (const double*)psi);
-    else k_clean_apply<float><<<grid, block, 0, s>>>(g, (float*)u, (float*)v, (const float*)psi);
+    if (dtype == 0) launch_pdl(k_clean_apply<double>, grid, block, s, g, (double*)u, (double*)v, (const double*)psi);
+    else launch_pdl(k_clean_apply<float>, grid, block, s, g, (float*)u, (float*)v, (const float*)psi);
 }
 
 }  // namespace b200cfd

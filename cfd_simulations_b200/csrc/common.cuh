@@ -5,7 +5,28 @@
 #include <stdint.h>
 #include <math.h>
 
+#include <cstdlib>
+
 namespace b200cfd {
+
+inline bool pdl_enabled() {
+    // OFF by default — measured on B200 (4096x1024 fp64, CUDA-graph replay): attribute alone 0.3032 vs 0.3030 ms/step
+    // (graph launches already hide the launch latency), with an early trigger 0.332 ms/step (waiting blocks of the next
+    // kernel take the slots of the running one).  B200CFD_PDL=1 turns it on for experiments.
+    static const bool on = getenv("B200CFD_PDL") != nullptr;
+    return on;
+}
+// <<<grid, block, 0, s>>> with the programmatic-stream-serialization attribute (see pdl_wait below)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 // Geometry + precomputed coefficients (host-computed in double with the reference's expressions so
 // the constants are bit-identical to the oracle's: v5.py:131-132,168-169,182-183,205-210).
@@ -120,5 +141,22 @@ __device__ __forceinline__ double block_sum(double v) {
 }
 
 __device__ __forceinline__ double bits_to_double(unsigned long long b) { return __longlong_as_double((long long)b); }
+
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------
+// The step is a chain of 7 kernels of 30-70 us (4096x1024) down to 6-40 us (600x180): launch latency and the drain /
+// ramp between two kernels are a visible share.  A kernel launched with launch_pdl() may be SCHEDULED while its
+// predecessor is still running; it must call pdl_wait() before it touches anything the predecessor reads or writes
+// (first statement of the kernel), which returns once the predecessor has completed and its writes are visible.
+// pdl_trigger() right after it lets the NEXT kernel of the chain be scheduled as soon as every block of this one is
+// resident.  Without the launch attribute both are no-ops, so the same kernels work from any launcher.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#ifndef B200CFD_PDL_EARLY_TRIGGER
+#define B200CFD_PDL_EARLY_TRIGGER 0   // measured on B200: triggering at kernel entry is SLOWER (4096x1024: 0.332 vs 0.302 ms/step)
+#endif
+__device__ __forceinline__ void pdl_trigger() {
+#if B200CFD_PDL_EARLY_TRIGGER
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
 
 }  // namespace b200cfd

@@ -127,6 +127,7 @@ __global__ void __launch_bounds__(FBT, 5)
 k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
                  T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const double* __restrict__ ibm,
                  const double* __restrict__ y, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    pdl_wait(); pdl_trigger();
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int cb = blockIdx.x * FCOLS;
     const int j0 = cb + 2 * threadIdx.x;
@@ -207,7 +208,7 @@ void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCt
     const int rpb = rows_per_block(g, n_sm);
     const dim3 grid((g.nx + FCOLS - 1) / FCOLS, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define PF(T, TAU) k_predictor_fast<T, TAU><<<grid, FBT, 0, s>>>(g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb)
+#define PF(T, TAU) launch_pdl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb)
     if (dtype == 0) { if (tau) PF(double, true); else PF(double, false); }
     else { if (tau) PF(float, true); else PF(float, false); }
 #undef PF
@@ -340,6 +341,7 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
                 const T* __restrict__ psi, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm,
                 const uint8_t* __restrict__ mask, const double* __restrict__ y, double* __restrict__ ke_part,
                 unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int own_c0 = blockIdx.x * FB_OWN + warp * FW_OWN;        // first column owned by this warp
@@ -521,7 +523,7 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
     int rpb;
     const dim3 grid = finalize_fast_grid(g, n_sm, &rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define FF(T, PSI) k_finalize_fast<T, PSI><<<grid, FBT, 0, s>>>(g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
+#define FF(T, PSI) launch_pdl(k_finalize_fast<T, PSI>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
     if (dtype == 0) { if (psi) FF(double, true); else FF(double, false); }
     else { if (psi) FF(float, true); else FF(float, false); }
 #undef FF
@@ -541,6 +543,7 @@ __global__ void __launch_bounds__(FBT, 4)
 k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint8_t* __restrict__ mask,
                        T* __restrict__ phi, T* __restrict__ div_out, T* __restrict__ ua, T* __restrict__ va,
                        double inv_dt, StepCtl* __restrict__ ctl, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+    pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int own_c0 = blockIdx.x * FB_OWN + warp * FW_OWN;        // first column owned by this warp
@@ -675,7 +678,7 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define DCF(T, DIV) k_div_rb1_correct_fast<T, DIV><<<grid, FBT, 0, s>>>(g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)
+#define DCF(T, DIV) launch_pdl(k_div_rb1_correct_fast<T, DIV>, grid, dim3(FBT), s, g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)
     if (dtype == 0) { if (div_out) DCF(double, true); else DCF(double, false); }
     else { if (div_out) DCF(float, true); else DCF(float, false); }
 #undef DCF

@@ -347,6 +347,7 @@ __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restric
 __global__ void k_ctl_reduce_end(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
                                  const unsigned long long* __restrict__ cnt_part, int n_part, double* red, int close_rb1,
                                  double tol, StepScalars* ring, int cap) {
+    pdl_wait(); pdl_trigger();
     ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol);
     if (threadIdx.x) return;
     ctl_end_step(c, cp, red, 1, ring, cap);
@@ -456,7 +457,7 @@ void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsi
 void launch_ctl_reduce_end(StepCtl* ctl, const CtlParams& cp, const double* ke_partials, const unsigned long long* cnt_partials,
                            int n_partials, double* red, int close_rb1, double tol, StepScalars* ring, int ring_cap,
                            cudaStream_t s) {
-    k_ctl_reduce_end<<<1, 256, 0, s>>>(ctl, cp, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, ring, ring_cap);
+    launch_pdl(k_ctl_reduce_end, dim3(1), dim3(256), s, ctl, cp, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, ring, ring_cap);
 }
 void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
                          int ring_cap, cudaStream_t s) {

@@ -123,6 +123,23 @@ __device__ __forceinline__ void block_atomic_max(double v, unsigned long long* d
     }
 }
 
+// Three block maxima of non-negative values with ONE barrier (1-D blocks of up to 32 warps): warp shuffles, one slot
+// per warp, thread 0 folds the warps and issues the atomics.
+__device__ __forceinline__ void block_atomic_max3(double a, double b, double c, unsigned long long* da,
+                                                  unsigned long long* db, unsigned long long* dc) {
+    __shared__ double s_m[3][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    a = warp_max(a); b = warp_max(b); c = warp_max(c);
+    if (lane == 0) { s_m[0][w] = a; s_m[1][w] = b; s_m[2][w] = c; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < nw; ++k) { a = fmax(a, s_m[0][k]); b = fmax(b, s_m[1][k]); c = fmax(c, s_m[2][k]); }
+        if (a > 0.0) atomicMax(da, (unsigned long long)__double_as_longlong(a));
+        if (b > 0.0) atomicMax(db, (unsigned long long)__double_as_longlong(b));
+        if (c > 0.0) atomicMax(dc, (unsigned long long)__double_as_longlong(c));
+    }
+}
+
 // Block sum with a fixed reduction tree (deterministic for a fixed launch shape); result valid in thread 0.
 __device__ __forceinline__ double block_sum(double v) {
     __shared__ double s_sum[32];

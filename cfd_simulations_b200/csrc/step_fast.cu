@@ -577,23 +577,29 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
             st2<T>(ua, kk, a.x, a.y); st2<T>(va, kk, b.x, b.y);
         }
         if (lo < hi) {                                             // warp-uniform
-            auto vrow = [&](int r) { return (inb && r >= 0 && r < g.ny) ? ld2<T>(vs, (long long)r * g.pitch + c0) : D2{0.0, 0.0}; };
-            auto urow = [&](int r) { return (inb && r >= 0 && r < g.ny) ? ld2<T>(us, (long long)r * g.pitch + c0) : D2{0.0, 0.0}; };
+            // Guard-free accessors: rows are clamped into [0, ny-1] and a lane outside the array reads a clamped column.
+            // Nothing read that way is ever used: D is forced to 0 on border rows / non-interior columns, and stores are
+            // owner-only.  (Selects and zero-fills per load were a quarter of this kernel's instructions.)
+            const int cs = min(max(c0, 0), g.nx - 2);
+            const T* __restrict__ usp = us + cs;
+            const T* __restrict__ vsp = vs + cs;
+            const int nym1 = g.ny - 1;
+            auto rowoff = [&](int r) { return (long long)min(max(r, 0), nym1) * g.pitch; };
+            auto vrow = [&](int r) { return ld2<T>(vsp, rowoff(r)); };
+            auto urow = [&](int r) { return ld2<T>(usp, rowoff(r)); };
             auto mrow = [&](int r) {
-                return (has_mask && inb && r >= 0 && r < g.ny) ? *reinterpret_cast<const uchar2*>(mask + (long long)r * g.pitch + c0)
-                                                               : make_uchar2(0, 0);
+                return has_mask ? *reinterpret_cast<const uchar2*>(mask + rowoff(r) + cs) : make_uchar2(0, 0);
             };
             // D of row r from its u* pair (x-neighbours by shuffle; the two halo lanes load theirs) and v* of rows r+1, r-1
             auto drow = [&](int r, const D2& uc, const D2& vN, const D2& vS) {
-                D2 d = {0.0, 0.0};
-                if (r >= 1 && r < g.ny - 1) {                       // warp-uniform
-                    double uW = shfl_up1(uc.y), uE = shfl_dn1(uc.x);
-                    const long long kr = (long long)r * g.pitch + c0;
-                    if (lane == 0 && xin) uW = ld(us, kr - 1);
-                    if (lane == 31 && yin) uE = ld(us, kr + 2);
-                    if (xin) d.x = div_raw<T>(g, uc.y, uW, vN.x, vS.x);
-                    if (yin) d.y = div_raw<T>(g, uE, uc.x, vN.y, vS.y);
-                }
+                const bool rin = r >= 1 && r < nym1;                // warp-uniform
+                double uW = shfl_up1(uc.y), uE = shfl_dn1(uc.x);
+                const long long kr = (long long)r * g.pitch + c0;
+                if (lane == 0 && xin && rin) uW = ld(us, kr - 1);
+                if (lane == 31 && yin && rin) uE = ld(us, kr + 2);
+                D2 d;
+                d.x = (xin && rin) ? div_raw<T>(g, uc.y, uW, vN.x, vS.x) : 0.0;
+                d.y = (yin && rin) ? div_raw<T>(g, uE, uc.x, vN.y, vS.y) : 0.0;
                 return d;
             };
             // phi of row i after the red (odd) then black (even) colour of the first iteration from phi = 0
@@ -632,9 +638,8 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
             for (; i <= hi; ++i) {
                 const long long k = (long long)i * g.pitch + c0;
                 if (inb && i + FPF < g.ny) { pf_l2(us + k + FPF * g.pitch); pf_l2(vs + k + FPF * g.pitch); }
-                const bool more = i < hi;
-                const D2 v_n3 = more ? vrow(i + 3) : D2{0.0, 0.0}, u_n2 = more ? urow(i + 2) : D2{0.0, 0.0};
-                const uchar2 mn2 = more ? mrow(i + 2) : make_uchar2(0, 0);
+                const D2 v_n3 = vrow(i + 3), u_n2 = urow(i + 2);     // (clamped rows: harmless on the last iterations)
+                const uchar2 mn2 = mrow(i + 2);
                 const D2 Dn = drow(i + 1, u_n, v_nn, v_c);
                 const D2 p_c = prow(i, Dm, Dc, Dn, mm, mc, mn);
                 if (owner && i >= lo && i < hi) {
@@ -652,8 +657,9 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
                         st2<T>(ua, k - g.pitch, axmy<T>(u_m.x, dt, gxx), axmy<T>(u_m.y, dt, gxy));
                         st2<T>(va, k - g.pitch, axmy<T>(v_m.x, dt, gyx), axmy<T>(v_m.y, dt, gyy));
                     }
-                    if (ownx) gmax = fmax(gmax, sqrt(Rnd<T>::r(Rnd<T>::r(gxx * gxx) + Rnd<T>::r(gyx * gyx))));
-                    if (owny) gmax = fmax(gmax, sqrt(Rnd<T>::r(Rnd<T>::r(gxy * gxy) + Rnd<T>::r(gyy * gyy))));
+                    // max |grad phi| = sqrt(max |grad phi|^2): the square root is taken once per thread after the loop
+                    if (ownx) gmax = fmax(gmax, Rnd<T>::r(Rnd<T>::r(gxx * gxx) + Rnd<T>::r(gyx * gyx)));
+                    if (owny) gmax = fmax(gmax, Rnd<T>::r(Rnd<T>::r(gxy * gxy) + Rnd<T>::r(gyy * gyy)));
                 }
                 Dm = Dc; Dc = Dn; v_m = v_c; v_c = v_n; v_n = v_nn; v_nn = v_n3; u_m = u_c; u_c = u_n; u_n = u_n2;
                 p_mm = p_m; p_m = p_c; mm = mc; mc = mn; mn = mn2;
@@ -661,9 +667,7 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
         }
     }
     if (ctl) {
-        block_atomic_max(dabs, &ctl->max_div_pre);
-        block_atomic_max(ch, &ctl->pois_change);
-        block_atomic_max(gmax, &ctl->max_grad);
+        block_atomic_max3(dabs, ch, sqrt(gmax), &ctl->max_div_pre, &ctl->pois_change, &ctl->max_grad);
     }
 }
 

@@ -32,6 +32,7 @@ struct b200cfd_handle {
     StepScalars* ring = nullptr;
     int ring_cap = 8192;
     void *ua = nullptr, *va = nullptr, *psi[2] = {nullptr, nullptr}, *tmp = nullptr;
+    double* nut_part = nullptr;           // LES: NUT_PARTS partial sums of nu_t (mean(nu_t) of adaptive_time_step)
     void *ub = nullptr, *vb = nullptr;   // second velocity pair: output of the clean sweep with the correction fused in
     double* ke_part = nullptr;
     double* red = nullptr;            // this slab's reduction vector (RED_N doubles)
@@ -132,6 +133,8 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     h->cp.hmin = h->g.hmin; h->cp.nu = cfg->nu; h->cp.av = cfg->av;
     h->cp.adaptive_dt = cfg->adaptive_dt; h->cp.initial_steps = cfg->initial_steps > 0 ? cfg->initial_steps : 1;
     h->cp.is_f32 = f32; h->cp.use_les = cfg->use_les;
+    h->cp.n_cells_global = (double)cfg->ny * (double)nxg;
+    if (cfg->use_les) { CUC(cudaMalloc(&h->nut_part, NUT_PARTS * sizeof(double))); CUC(cudaMemset(h->nut_part, 0, NUT_PARTS * sizeof(double))); }
     h->clean = clean_plan(h->g, cfg->dtype, h->n_sm);
     const size_t n = (size_t)cfg->ny * cfg->nx, fb = n * h->es;
     CUC(cudaMalloc(&h->ctl, sizeof(StepCtl)));
@@ -153,7 +156,7 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     CUC(cudaMalloc(&h->red, sizeof(double) * RED_N));
     CUC(cudaMemset(h->red, 0, sizeof(double) * RED_N));
     CUC(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
-    launch_ctl_init(h->ctl, h->cp, 0, 0, nullptr);
+    launch_ctl_init(h->ctl, h->cp, 0, 0, nullptr, nullptr);
     CUC(cudaDeviceSynchronize());
 #undef CUC
     *out = h;
@@ -167,7 +170,7 @@ int b200cfd_destroy(b200cfd_handle* h) {
     if (h->begin_graph) cudaGraphExecDestroy(h->begin_graph);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->tb) poisson_tb_destroy(h->tb);
-    cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->ub); cudaFree(h->vb); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
+    cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->ub); cudaFree(h->vb); cudaFree(h->nut_part); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
     cudaFree(h->tmp); cudaFree(h->ke_part); cudaFree(h->cnt_part); cudaFree(h->red); cudaFree(h->flags);
     delete h;
     return B200CFD_OK;
@@ -203,7 +206,8 @@ int b200cfd_set_step(b200cfd_handle* h, int64_t step, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     CU(h, cudaSetDevice(h->device));
     launch_max_abs2(h->cfg.dtype, h->g, h->u, h->v, h->ctl, s);
-    launch_ctl_init(h->ctl, h->cp, (long long)step, 1, s);
+    if (h->cfg.use_les && h->nu_t) launch_field_sum(h->cfg.dtype, h->g, h->nu_t, h->nut_part, s);
+    launch_ctl_init(h->ctl, h->cp, (long long)step, 1, h->cfg.use_les ? h->nut_part : nullptr, s);
     CHECK_LAUNCH(h);
     h->step = step;
     return B200CFD_OK;
@@ -320,7 +324,11 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     int nl = 0, pi = 0, close_rb1 = 0;
     const void* nut = nullptr;
     prof_mark(h, nullptr, s, pi);
-    if (c.use_les) { launch_smagorinsky(dt, h->g, h->u, h->v, h->nu_t, c.cs, s); nut = h->nu_t; ++nl; }
+    if (c.use_les) {
+        launch_smagorinsky(dt, h->g, h->u, h->v, h->nu_t, c.cs, s);
+        launch_field_sum(dt, h->g, h->nu_t, h->nut_part, s);      // mean(nu_t) for the NEXT step's adaptive dt (v5.py:323)
+        nut = h->nu_t; nl += 2;
+    }
     if (h->fast) launch_predictor_fast(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, h->ibm, h->y, h->flags, h->n_sm, s);
     else launch_predictor(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, nut, h->ibm, h->y, s);
     ++nl;
@@ -348,8 +356,8 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     else launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s);
     ++nl;
     prof_mark(h, "finalize", s, pi);
-    if (close) launch_ctl_reduce_end(h->ctl, h->cp, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->ring, h->ring_cap, s);
-    else launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, s);
+    if (close) launch_ctl_reduce_end(h->ctl, h->cp, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->nut_part, h->ring, h->ring_cap, s);
+    else launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->nut_part, s);
     ++nl;
     prof_mark(h, "ctl", s, pi);
     if (h->profiling) ++h->prof_steps;
@@ -440,7 +448,8 @@ int b200cfd_set_step_global(b200cfd_handle* h, int64_t step, double max_abs_u, d
     CU(h, cudaMemcpyAsync(&h->ctl->max_u, &bits[0], 8, cudaMemcpyHostToDevice, s));
     CU(h, cudaMemcpyAsync(&h->ctl->max_v, &bits[1], 8, cudaMemcpyHostToDevice, s));
     CU(h, cudaStreamSynchronize(s));
-    launch_ctl_init(h->ctl, h->cp, (long long)step, 1, s);
+    // (LES on slabs: mean(nu_t) restarts from 0 here and is exact again from the first step taken, which all_gathers it)
+    launch_ctl_init(h->ctl, h->cp, (long long)step, 1, nullptr, s);
     CHECK_LAUNCH(h);
     h->step = step;
     return B200CFD_OK;

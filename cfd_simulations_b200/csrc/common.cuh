@@ -73,7 +73,7 @@ struct StepCtl {
 
 // Per-rank reduction vector exchanged between slabs at the end of a step (all_gather of RED_N doubles per rank).
 enum { RED_MAX_DIV_PRE = 0, RED_MAX_GRAD, RED_MAX_DIV_POST, RED_MAX_VORT, RED_MAX_U, RED_MAX_V, RED_POIS_CHANGE,
-       RED_NONFINITE, RED_ENERGY_SUM, RED_ENERGY_CNT, RED_N = 16 };
+       RED_NONFINITE, RED_ENERGY_SUM, RED_ENERGY_CNT, RED_NUT_SUM, RED_N = 16 };
 
 struct StepScalars {   // must match b200cfd_step_scalars (12 doubles)
     double dt, max_div_pre, max_grad_phi, max_div_post, max_vorticity, mean_energy, max_abs_u, max_abs_v,

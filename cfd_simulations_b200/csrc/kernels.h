@@ -16,7 +16,11 @@ struct Phys {
 struct CtlParams {
     double cfl_target, dt_min, dt_max, dt_base, hmin, nu, av;
     int adaptive_dt, initial_steps, is_f32, use_les;
+    double n_cells_global;      // ny * nx_global: denominator of mean(nu_t) (v5.py:323)
 };
+#define NUT_PARTS 256           // fixed number of partial sums of nu_t (deterministic two-stage reduction)
+// sum of nu_t over the OWNED columns into NUT_PARTS partials (LES only; feeds adaptive_time_step's mean(nu_t))
+void launch_field_sum(int dtype, const Geom& g, const void* f, double* partials, cudaStream_t s);
 
 // ---- unit kernels (one per reference @njit function) -------------------------------------------
 void launch_supg_tau(int dtype, const Geom& g, const void* u, const void* v, void* tau, double dt, double nu_eff,
@@ -47,13 +51,14 @@ void launch_finalize(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, cons
 int finalize_num_partials(const Geom& g);
 // compute_vorticity (v5.py:365-373), for the snapshot writer
 void launch_vorticity(int dtype, const Geom& g, const void* u, const void* v, const uint8_t* mask, void* w, cudaStream_t s);
-void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s);
+void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, const double* nut_partials,
+                     cudaStream_t s);
 void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
-                             int n_partials, double* red, int close_rb1, double tol, cudaStream_t s);
+                             int n_partials, double* red, int close_rb1, double tol, const double* nut_partials, cudaStream_t s);
 // one GPU: reduce_local + end_step in one launch
 void launch_ctl_reduce_end(StepCtl* ctl, const CtlParams& cp, const double* ke_partials, const unsigned long long* cnt_partials,
-                           int n_partials, double* red, int close_rb1, double tol, StepScalars* ring, int ring_cap,
-                           cudaStream_t s);
+                           int n_partials, double* red, int close_rb1, double tol, const double* nut_partials,
+                           StepScalars* ring, int ring_cap, cudaStream_t s);
 void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
                          int ring_cap, cudaStream_t s);
 // ---- x-slab halos: strided columns <-> contiguous buffer [ny][ncols] (halo.cu) -------------------

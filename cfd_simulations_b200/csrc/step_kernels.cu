@@ -261,11 +261,13 @@ __device__ void ctl_prepare(StepCtl* c, const CtlParams& cp) {
     c->pois_change = 0ull; c->pois_last = 0.0; c->pois_iters = 0; c->pois_done = 0; c->pois_blocks_done = 0u;
 }
 
-__global__ void k_ctl_init(StepCtl* c, CtlParams cp, long long step, int use_measured_max) {
+__global__ void k_ctl_init(StepCtl* c, CtlParams cp, long long step, int use_measured_max, const double* __restrict__ nut_part) {
     if (threadIdx.x || blockIdx.x) return;
     c->step = step;
     if (use_measured_max) { c->in_max_u = bits_to_double(c->max_u); c->in_max_v = bits_to_double(c->max_v); }
-    c->in_mean_nut = 0.0;
+    double nut = 0.0;                                        // LES: mean of the nu_t attribute as it stands (v5.py:323)
+    if (cp.use_les && nut_part) for (int k = 0; k < NUT_PARTS; ++k) nut += nut_part[k];
+    c->in_mean_nut = nut / cp.n_cells_global;
     ctl_prepare(c, cp);
 }
 
@@ -276,7 +278,8 @@ __global__ void k_ctl_zero_max(StepCtl* c) { if (!threadIdx.x && !blockIdx.x) { 
 // close_rb1: the "as executed" Poisson bookkeeping (what k_rb1_close does) is folded in here, saving a launch per step.
 __device__ __forceinline__ void ctl_reduce_local(StepCtl* c, const double* __restrict__ ke_part,
                                                  const unsigned long long* __restrict__ cnt_part, int n_part,
-                                                 double* __restrict__ red, int close_rb1, double tol) {
+                                                 double* __restrict__ red, int close_rb1, double tol,
+                                                 const double* __restrict__ nut_part) {
     __shared__ double s_e[256];
     __shared__ unsigned long long s_c[256];
     double e = 0.0; unsigned long long n = 0;
@@ -302,7 +305,10 @@ __device__ __forceinline__ void ctl_reduce_local(StepCtl* c, const double* __res
     red[RED_NONFINITE] = (double)c->nonfinite;
     red[RED_ENERGY_SUM] = s_e[0];
     red[RED_ENERGY_CNT] = (double)s_c[0];
-    for (int k = RED_ENERGY_CNT + 1; k < RED_N; ++k) red[k] = 0.0;
+    double nut = 0.0;                                        // LES: fixed-order sum of the nu_t partials
+    if (nut_part) for (int k = 0; k < NUT_PARTS; ++k) nut += nut_part[k];
+    red[RED_NUT_SUM] = nut;
+    for (int k = RED_NUT_SUM + 1; k < RED_N; ++k) red[k] = 0.0;
 }
 
 // End of a step, part 2: combine the reduction vectors of all slabs (max is exact and order independent; the energy sum
@@ -310,11 +316,11 @@ __device__ __forceinline__ void ctl_reduce_local(StepCtl* c, const double* __res
 __device__ __forceinline__ void ctl_end_step(StepCtl* c, const CtlParams& cp, const double* gathered, int nranks,
                                              StepScalars* ring, int cap) {
     double m[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    double es = 0.0, ec = 0.0;
+    double es = 0.0, ec = 0.0, nut = 0.0;
     for (int r = 0; r < nranks; ++r) {
         const double* v = gathered + (size_t)r * RED_N;
         for (int k = 0; k < 8; ++k) m[k] = fmax(m[k], v[k]);
-        es += v[RED_ENERGY_SUM]; ec += v[RED_ENERGY_CNT];
+        es += v[RED_ENERGY_SUM]; ec += v[RED_ENERGY_CNT]; nut += v[RED_NUT_SUM];
     }
     StepScalars r;
     r.dt = c->dt;
@@ -331,12 +337,14 @@ __device__ __forceinline__ void ctl_end_step(StepCtl* c, const CtlParams& cp, co
     r.step = (double)c->step;
     ring[(int)(c->step % cap)] = r;
     c->in_max_u = r.max_abs_u; c->in_max_v = r.max_abs_v;
+    if (cp.use_les) c->in_mean_nut = nut / cp.n_cells_global;     // np.mean(self.nu_t) of the step just taken (v5.py:323)
     c->step += 1;
     ctl_prepare(c, cp);
 }
 __global__ void k_ctl_reduce_local(StepCtl* c, const double* __restrict__ ke_part, const unsigned long long* __restrict__ cnt_part,
-                                   int n_part, double* __restrict__ red, int close_rb1, double tol) {
-    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol);
+                                   int n_part, double* __restrict__ red, int close_rb1, double tol,
+                                   const double* __restrict__ nut_part) {
+    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol, nut_part);
 }
 __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restrict__ gathered, int nranks,
                                StepScalars* ring, int cap) {
@@ -346,9 +354,9 @@ __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restric
 // one GPU: both parts in one launch (thread 0 wrote red itself, so it can read it back without a fence)
 __global__ void k_ctl_reduce_end(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
                                  const unsigned long long* __restrict__ cnt_part, int n_part, double* red, int close_rb1,
-                                 double tol, StepScalars* ring, int cap) {
+                                 double tol, const double* __restrict__ nut_part, StepScalars* ring, int cap) {
     pdl_wait(); pdl_trigger();
-    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol);
+    ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol, nut_part);
     if (threadIdx.x) return;
     ctl_end_step(c, cp, red, 1, ring, cap);
 }
@@ -392,6 +400,21 @@ void launch_smagorinsky(int dtype, const Geom& g, const void* u, const void* v, 
     DISPATCH(dtype,
              (k_smagorinsky<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, (double*)nu_t, csd2)),
              (k_smagorinsky<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, (float*)nu_t, csd2)));
+}
+// Sum of a field over the owned columns, NUT_PARTS fixed partials (block b sums rows b, b + NUT_PARTS, ...): the result
+// does not depend on scheduling.  Only used for mean(nu_t) when LES is on.
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_field_sum(Geom g, const T* __restrict__ f, double* __restrict__ partials) {
+    double acc = 0.0;
+    for (int i = blockIdx.x; i < g.ny; i += NUT_PARTS)
+        for (int j = g.own0 + threadIdx.x; j < g.own1; j += 256) acc += (double)f[(long long)i * g.pitch + j];
+    const double bs = block_sum(acc);
+    if (threadIdx.x == 0) partials[blockIdx.x] = bs;
+}
+void launch_field_sum(int dtype, const Geom& g, const void* f, double* partials, cudaStream_t s) {
+    DISPATCH(dtype, (k_field_sum<double><<<NUT_PARTS, 256, 0, s>>>(g, (const double*)f, partials)),
+             (k_field_sum<float><<<NUT_PARTS, 256, 0, s>>>(g, (const float*)f, partials)));
 }
 void launch_apply_bc(int dtype, const Geom& g, void* u, void* v, const double* y, double V_inf, double y_max,
                      long long step, cudaStream_t s) {
@@ -447,17 +470,18 @@ void launch_vorticity(int dtype, const Geom& g, const void* u, const void* v, co
              (k_vorticity<double><<<grid2d(g), kBlock, 0, s>>>(g, (const double*)u, (const double*)v, mask, (double*)w)),
              (k_vorticity<float><<<grid2d(g), kBlock, 0, s>>>(g, (const float*)u, (const float*)v, mask, (float*)w)));
 }
-void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, cudaStream_t s) {
-    k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max);
+void launch_ctl_init(StepCtl* ctl, const CtlParams& cp, long long step, int use_measured_max, const double* nut_partials,
+                     cudaStream_t s) {
+    k_ctl_init<<<1, 32, 0, s>>>(ctl, cp, step, use_measured_max, nut_partials);
 }
 void launch_ctl_reduce_local(StepCtl* ctl, const double* ke_partials, const unsigned long long* cnt_partials,
-                             int n_partials, double* red, int close_rb1, double tol, cudaStream_t s) {
-    k_ctl_reduce_local<<<1, 256, 0, s>>>(ctl, ke_partials, cnt_partials, n_partials, red, close_rb1, tol);
+                             int n_partials, double* red, int close_rb1, double tol, const double* nut_partials, cudaStream_t s) {
+    k_ctl_reduce_local<<<1, 256, 0, s>>>(ctl, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, nut_partials);
 }
 void launch_ctl_reduce_end(StepCtl* ctl, const CtlParams& cp, const double* ke_partials, const unsigned long long* cnt_partials,
-                           int n_partials, double* red, int close_rb1, double tol, StepScalars* ring, int ring_cap,
-                           cudaStream_t s) {
-    launch_pdl(k_ctl_reduce_end, dim3(1), dim3(256), s, ctl, cp, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, ring, ring_cap);
+                           int n_partials, double* red, int close_rb1, double tol, const double* nut_partials,
+                           StepScalars* ring, int ring_cap, cudaStream_t s) {
+    launch_pdl(k_ctl_reduce_end, dim3(1), dim3(256), s, ctl, cp, ke_partials, cnt_partials, n_partials, red, close_rb1, tol, nut_partials, ring, ring_cap);
 }
 void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gathered, int nranks, StepScalars* ring,
                          int ring_cap, cudaStream_t s) {

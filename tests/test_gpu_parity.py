@@ -339,3 +339,34 @@ def test_odd_and_ragged_grids_vs_oracle(nx, ny):
         for key, idx in (("max_div_pre", 1), ("max_grad_phi", 2), ("max_div_post", 3), ("max_vorticity", 4), ("mean_energy", 5)):
             assert abs(a[key] - b[idx]) <= 1e-9 * max(abs(b[idx]), 1e-30), (key, k)
     sg.close()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_les_branch_vs_oracle(orc, f32):
+    """a15: use_les=True (Smagorinsky nu_t, v5.py:96-110,381-388) through whole time steps, including steps past 1000
+    where adaptive_time_step reads mean(nu_t) (v5.py:323) — on a grid fine enough that the viscous limit, not the clip,
+    sets dt, so a wrong mean would change dt."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    from oracle.solver import OracleTurbulentSolver
+    h = 4.5e-4            # 0.4 h^2 / nu_total = 3.0e-5 < 0.1 h / |u|max and < the 1e-4 clip
+    cfg = OptimizedTurbulentConfig(nx=150, ny=46, memory_efficient=f32, use_les=True, smagorinsky_constant=0.5,
+                                   x_max=149 * h, y_max=45 * h, cylinder_center=(30 * h, 22.5 * h), R_cylinder=6 * h)
+    so, sg = OracleTurbulentSolver(cfg), OptimizedTurbulentSolver(cfg)
+    tol = TOL["f32" if f32 else "f64"]
+    for start, n in ((0, 12), (995, 12)):
+        if start:
+            so.step = start
+            sg.u, sg.v = so.u, so.v
+            sg.nu_t = so.nu_t
+            sg.step = start
+        dts_o = [float(so.time_step()) for _ in range(n)]
+        sg.advance(n)
+        sg._sync_scalars()
+        dts_g = [r["dt"] for r in sg.scalars[-n:]]
+        assert np.allclose(dts_g, dts_o, rtol=1e-12 if not f32 else 1e-6), (start, dts_g, dts_o)
+        assert rel_l2(sg.u, so.u) <= tol * (1 if not f32 else 3) and rel_l2(sg.v, so.v) <= tol * (1 if not f32 else 3)
+        assert rel_l2(sg.nu_t, so.nu_t) <= tol * (1 if not f32 else 3)
+    # past step 1000 dt is neither the warm-up value nor the 1e-4 clip: the limits that read mean(nu_t) / max|u| are active
+    assert all(d < 0.9e-4 for d in dts_o[-5:]) and any(2.5e-5 < d < 3.04e-5 for d in dts_o)
+    sg.close()

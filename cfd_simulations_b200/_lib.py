@@ -74,7 +74,7 @@ EXPORTS = [
     "b200cfd_k_supg_tau", "b200cfd_k_convection", "b200cfd_k_laplacian", "b200cfd_k_divergence",
     "b200cfd_k_gradient", "b200cfd_k_smagorinsky", "b200cfd_k_vorticity", "b200cfd_k_apply_bc", "b200cfd_k_apply_ibm",
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
-    "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len",
+    "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len", "b200cfd_poisson_change_ptr",
     "b200cfd_set_step_global", "b200cfd_pack_columns", "b200cfd_unpack_columns",
 ]
 
@@ -125,6 +125,8 @@ def load():
     lib.b200cfd_step_end.argtypes = [vp, vp, i32, vp]
     lib.b200cfd_reduction_ptr.argtypes = [vp]
     lib.b200cfd_reduction_ptr.restype = vp
+    lib.b200cfd_poisson_change_ptr.argtypes = [vp]
+    lib.b200cfd_poisson_change_ptr.restype = vp
     lib.b200cfd_set_step_global.argtypes = [vp, i64, dbl, dbl, vp]
     lib.b200cfd_pack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
     lib.b200cfd_unpack_columns.argtypes = [vp, vp, i32, i32, vp, vp]

@@ -438,6 +438,7 @@ int b200cfd_step_end(b200cfd_handle* h, const double* gathered, int nranks, void
 }
 void* b200cfd_reduction_ptr(b200cfd_handle* h) { return h ? (void*)h->red : nullptr; }
 int b200cfd_reduction_len(void) { return RED_N; }
+void* b200cfd_poisson_change_ptr(b200cfd_handle* h) { return h ? (void*)&h->ctl->pois_last : nullptr; }
 // set_step for slabs: the caller supplies the GLOBAL post-clip maxima adaptive_time_step needs (v5.py:322)
 int b200cfd_set_step_global(b200cfd_handle* h, int64_t step, double max_abs_u, double max_abs_v, void* stream) {
     if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");

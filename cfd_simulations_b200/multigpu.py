@@ -179,6 +179,20 @@ class LocalSlabs:
                 b._halo.pack(fb, pb.own0, pb.send_left, b._halo.sbuf_l[k])
                 a._halo.unpack(fa, pa.own1, pa.halo_right, b._halo.sbuf_l[k])
 
+    def solve_pressure(self, div_global, max_iter, tol, omega=1.0):
+        """The slab-decomposed "as written" Poisson solve (solver.solve_pressure_slabs) with the collectives emulated:
+        returns (global phi, iterations, last change)."""
+        S = self.slabs
+        rhs = []
+        for s in S:
+            p = s.plan
+            rhs.append(torch.as_tensor(np.ascontiguousarray(div_global[:, p.x_offset:p.x_offset + p.nx_local]),
+                                       dtype=s._d["phi"].dtype).to(s.device))
+        it, last = slab_poisson(S, rhs, int(max_iter), float(tol), float(omega),
+                                exchange=lambda: self.refresh_halos(names=("phi",)),
+                                reduce_max=lambda parts: torch.stack(parts).max(dim=0).values)
+        return self.gather("phi"), it, last
+
     def set_step(self, step):
         S = self.slabs
         hv = [s._local_health() for s in S]
@@ -207,3 +221,55 @@ class LocalSlabs:
     def close(self):
         for s in self.slabs:
             s.close()
+
+
+def slab_poisson(slabs, rhs, max_iter, tol, omega, exchange, reduce_max):
+    """Control flow of the slab-decomposed red-black Poisson solve, shared by a torchrun rank (`slabs` = [its solver])
+    and LocalSlabs (`slabs` = all of them).  exchange(): refresh the phi halos of every slab.  reduce_max(list of one
+    1-D device tensor per local slab) -> tensor of the GLOBAL per-iteration maxima.  Returns (iterations done, last
+    max|dphi|) with the reference's meaning (v5.py:212-225): the iteration whose change falls below `tol` is the last."""
+    hl, hr = slabs[0]._halo_req
+    nr = slabs[0]._nranks
+    T = max(1, min(hl, hr) // 2) if nr > 1 else 64          # iterations per halo refresh (validity shrinks 2 columns each)
+    views = [device_view(s._lib.b200cfd_poisson_change_ptr(s._h), 1, s.device) for s in slabs]
+    for s in slabs:
+        s._d["phi"].zero_()                                   # v5.py:331
+    check_tol = tol > 0.0
+    backups = [torch.empty_like(s._d["phi"]) for s in slabs] if check_tol else None
+    chg = [torch.zeros(T, dtype=torch.float64, device=s.device) for s in slabs]
+
+    def run(n, record):
+        for k in range(n):
+            for i, s in enumerate(slabs):
+                s._poisson_iterations(rhs[i], 1, omega)
+                if record:
+                    chg[i][k:k + 1].copy_(views[i])
+    it, last = 0, 0.0
+    while it < max_iter:
+        m = min(T, max_iter - it)
+        if check_tol:
+            for s, b in zip(slabs, backups):
+                b.copy_(s._d["phi"])
+        run(m, True)
+        g = None
+        stop = None
+        if check_tol or it + m >= max_iter:
+            g = reduce_max([c[:m] for c in chg]).tolist()     # one collective + one host read per chunk
+            last = g[m - 1]
+        if check_tol:
+            for k, c in enumerate(g):
+                if c < tol:
+                    stop = k
+                    break
+        if stop is not None:
+            if stop + 1 < m:                                  # overshot: replay the chunk up to the stopping iteration
+                for s, b in zip(slabs, backups):
+                    s._d["phi"].copy_(b)
+                run(stop + 1, False)
+            it += stop + 1
+            last = g[stop]
+            exchange()
+            break
+        it += m
+        exchange()
+    return it, last

@@ -69,6 +69,7 @@ class OptimizedTurbulentSolver:
             hl, hr = C.c_int(0), C.c_int(0)
             probe = make_c_config(cfg, cfg.ny, cfg.nx, poisson_mode, cleandiv_mode, omega, clean_iters)
             check(self._lib.b200cfd_required_halo(C.byref(probe), C.byref(hl), C.byref(hr)))
+        self._halo_req = (hl.value, hr.value)       # the same numbers on every rank
         self.plan = plan = multigpu.make_plan(cfg.nx, self._nranks, self._rank, hl.value, hr.value)
         cols = None if nranks == 1 else (plan.x_offset, plan.nx_local)
         npdt = cfg.field_dtype
@@ -111,7 +112,7 @@ class OptimizedTurbulentSolver:
         self.scalars = []            # list of dicts, one per step (the five logged values + dt ...)
         self._energy_history = []
         self._times = []
-        self._halo = None
+        self._halo = self._phi_halo = None
         if self._nranks > 1:
             n_red = int(self._lib.b200cfd_reduction_len())
             self._red = multigpu.device_view(self._lib.b200cfd_reduction_ptr(self._h), n_red, dev)
@@ -290,6 +291,9 @@ class OptimizedTurbulentSolver:
         """v5.py:328-347: zero phi, then the configured Poisson solve on `div_u_star` (numpy or CUDA tensor)."""
         cfg = self.config
         t = self._d["phi"]
+        if self._nranks > 1:
+            raise B200CFDError("solve_pressure_fast is the single-slab entry point: on x-slabs use solve_pressure_slabs "
+                               "(halo refresh + all-reduced max|dphi|)")
         if isinstance(div_u_star, torch.Tensor):
             rhs = div_u_star.to(device=self.device, dtype=t.dtype).contiguous()
         else:
@@ -304,6 +308,60 @@ class OptimizedTurbulentSolver:
             int(temporal_depth), C.byref(it), C.byref(last), _stream_ptr(self.device)), self._h)
         out = t if isinstance(div_u_star, torch.Tensor) else t.cpu().numpy()
         return (out, it.value, last.value) if return_info else out
+
+    # ---- iterative Poisson across x-slabs (halo refresh per pass + all-reduced residual) ----
+    def _poisson_iterations(self, rhs, n, omega):
+        """n plain red-black iterations of solve_pressure_gauss_seidel_fast on the LOCAL array (owned columns + halos),
+        no tolerance stop, no host synchronisation; max|dphi| of the last one stays on the device."""
+        cfg = self.config
+        check(self._lib.b200cfd_poisson(
+            self._h, self._d["phi"].data_ptr(), rhs.data_ptr(), self._d["mask"].data_ptr(), cfg.dx, cfg.dy, float(cfg.dt),
+            _lib.POISSON_AS_WRITTEN, int(n), 0.0, float(omega), 1, None, None, _stream_ptr(self.device)), self._h)
+
+    def _phi_exchanger(self):
+        if self._phi_halo is None and self._nranks > 1:
+            from . import multigpu
+            lib, h, dev = self._lib, self._h, self.device
+            sp = lambda: _stream_ptr(dev)
+            tdt = self._d["phi"].dtype
+            self._phi_halo = multigpu.HaloExchanger(
+                self.plan, self.config.ny, 1, alloc=lambda shape: torch.empty(shape, dtype=tdt, device=dev),
+                pack=lambda f, j0, n, out: check(lib.b200cfd_pack_columns(h, f.data_ptr(), j0, n, out.data_ptr(), sp()), h),
+                unpack=lambda f, j0, n, src: check(lib.b200cfd_unpack_columns(h, f.data_ptr(), j0, n, src.data_ptr(), sp()), h),
+                group=self._group)
+        return self._phi_halo
+
+    def solve_pressure_slabs(self, div_u_star, max_iter=None, tol=None, omega=None, return_info=False):
+        """solve_pressure_fast / solve_pressure_gauss_seidel_fast "as written" (v5.py:202-226, 328-347) on a grid that is
+        slab-decomposed over the ranks.  `div_u_star`: this rank's LOCAL (ny, nx_local) right-hand side, halo columns
+        included (`set_global`-style slice of the global array), numpy or CUDA tensor.  Communication-avoiding: the halos
+        are refreshed (NCCL send/recv) once per T = min(halo)/2 iterations, the region of validity shrinking by one column
+        per colour sweep in between; in tolerance mode the per-iteration max|dphi| of a chunk is all-reduced (MAX) in ONE
+        collective and, if the stopping iteration lies inside the chunk, the chunk is replayed up to exactly that
+        iteration — so iterates, iteration count and last change are those of the single-GPU solve."""
+        from . import multigpu
+        import torch.distributed as dist
+        cfg, t = self.config, self._d["phi"]
+        if isinstance(div_u_star, torch.Tensor):
+            rhs = div_u_star.to(device=self.device, dtype=t.dtype).contiguous()
+        else:
+            rhs = torch.as_tensor(np.ascontiguousarray(div_u_star), dtype=t.dtype).to(self.device)
+        if tuple(rhs.shape) != tuple(t.shape):
+            raise ValueError(f"local right-hand side must have the slab shape {tuple(t.shape)}, got {tuple(rhs.shape)}")
+        ex = self._phi_exchanger()
+
+        def reduce_max(parts):
+            g = parts[0].clone()
+            if self._nranks > 1:
+                dist.all_reduce(g, op=dist.ReduceOp.MAX, group=self._group)
+            return g
+
+        it, last = multigpu.slab_poisson(
+            [self], [rhs], int(cfg.pressure_iterations if max_iter is None else max_iter),
+            float(cfg.pressure_tolerance if tol is None else tol), float(self._ccfg.omega if omega is None else omega),
+            exchange=(lambda: ex.exchange([t])) if ex is not None else (lambda: None), reduce_max=reduce_max)
+        out = t if isinstance(div_u_star, torch.Tensor) else t.cpu().numpy()
+        return (out, it, last) if return_info else out
 
     def solve_pressure_iterative(self, div_u_star, max_iter=500, tol=1e-7, omega=1.5, return_info=False):
         """v2.py:284-306 (RobustTurbulentSolver.solve_pressure_iterative; v1.py:275-297 with 200 / 1e-6): the SOR fallback

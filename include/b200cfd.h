@@ -117,6 +117,10 @@ int   b200cfd_required_halo(const b200cfd_config* cfg, int* left, int* right);
 int   b200cfd_step_begin(b200cfd_handle* h, int use_graph, void* stream);
 int   b200cfd_step_end(b200cfd_handle* h, const double* gathered_dev, int nranks, void* stream);
 void* b200cfd_reduction_ptr(b200cfd_handle* h);
+/* Device address of one double: max|dphi| over the OWNED cells of the last completed red-black iteration of
+ * b200cfd_poisson (the reference's max_change, v5.py:212-225).  The slab Poisson solve all-reduces (MAX) it over the ranks
+ * (NCCL) instead of reading it back per iteration: see OptimizedTurbulentSolver.solve_pressure_slabs. */
+void* b200cfd_poisson_change_ptr(b200cfd_handle* h);
 int   b200cfd_reduction_len(void);
 /* self.step = step with the GLOBAL max|u|, max|v| of the state (what adaptive_time_step reads). Synchronises. */
 int   b200cfd_set_step_global(b200cfd_handle* h, int64_t step, double max_abs_u, double max_abs_v, void* stream);

@@ -42,6 +42,39 @@ def test_local_slabs_match_single_slab(nslabs, f32):
     one.close(); many.close()
 
 
+def _poisson_case(nx=1200, ny=160):
+    cfg = _cfg(nx, ny)
+    div = 0.1 * np.random.default_rng(11).standard_normal((ny, nx))
+    return cfg, div
+
+
+@pytest.mark.parametrize("nslabs", [2, 3])
+def test_local_slabs_poisson_matches_single_slab(nslabs):
+    """the iterative ("as written") red-black Poisson solve on slabs — halo refresh every T iterations,
+    per-iteration max|dphi| reduced over the slabs, exact stop — must give the single-slab iterates, iteration count and
+    last change, for fixed counts that are not multiples of the refresh period and in tolerance mode."""
+    from cfd_simulations_b200.multigpu import LocalSlabs
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg, div = _poisson_case()
+    one = OptimizedTurbulentSolver(cfg)
+    many = LocalSlabs(cfg, nslabs)
+    single = lambda iters, tol, omega: one.solve_pressure_fast(div, mode="as_written", max_iter=iters, tol=tol, omega=omega,
+                                                               temporal_depth=1, return_info=True)
+    for omega, iters in ((1.0, 23), (1.5, 16), (1.0, 1)):
+        p1, it1, l1 = single(iters, 0.0, omega)
+        pm, itm, lm = many.solve_pressure(div, iters, 0.0, omega)
+        assert itm == iters and np.array_equal(pm, p1), (omega, iters, rel_l2(pm, p1))
+        assert lm == l1
+    # tolerance mode: a tolerance between the changes of iterations 37 and 38 stops both after exactly 38 iterations
+    l37, l38 = single(37, 0.0, 1.0)[2], single(38, 0.0, 1.0)[2]
+    assert l38 < l37
+    tol = 0.5 * (l37 + l38)
+    p1, it1, l1 = single(5000, tol, 1.0)
+    pm, itm, lm = many.solve_pressure(div, 5000, tol, 1.0)
+    assert it1 == 38 and itm == 38 and lm == l1 and np.array_equal(pm, p1)
+    one.close(); many.close()
+
+
 def test_pack_unpack_columns_roundtrip():
     import ctypes as C
     import torch
@@ -72,9 +105,18 @@ def _nccl_worker(rank, world, port, out):
         s.advance(15)
         res = {k: s.gather(k) for k in ("u", "v", "phi")}
         s._sync_scalars()
+        # iterative Poisson on the slabs: NCCL halo refresh + all_reduce(MAX) of the per-iteration change
+        _, div = _poisson_case(1600, 128)
+        p = s.plan
+        loc = div[:, p.x_offset:p.x_offset + p.nx_local]
+        _, itf, lf = s.solve_pressure_slabs(loc, max_iter=23, tol=0.0, omega=1.0, return_info=True)
+        phi_fixed = s.gather("phi")
+        _, itt, lt = s.solve_pressure_slabs(loc, max_iter=5000, tol=float(out["tol"]), omega=1.0, return_info=True)
+        phi_tol = s.gather("phi")
         if rank == 0:
             out["fields"] = res
             out["scalars"] = s.scalars[-1]
+            out["poisson"] = {"fixed": (phi_fixed, itf, lf), "tol": (phi_tol, itt, lt)}
         s.close()
     finally:
         dist.destroy_process_group()
@@ -89,6 +131,16 @@ def test_nccl_slabs_match_single_gpu():
     world = min(n, 4)
     ctx = mp.get_context("spawn")
     out = ctx.Manager().dict()
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    ref = OptimizedTurbulentSolver(_cfg(1600, 128))
+    _, div = _poisson_case(1600, 128)
+    single = lambda iters, tol: ref.solve_pressure_fast(div, mode="as_written", max_iter=iters, tol=tol, omega=1.0,
+                                                        temporal_depth=1, return_info=True)
+    out["tol"] = 0.5 * (single(37, 0.0)[2] + single(38, 0.0)[2])
+    pf = single(23, 0.0)
+    pt = single(5000, float(out["tol"]))
+    pf, pt = (pf[0].copy(), pf[1], pf[2]), (pt[0].copy(), pt[1], pt[2])
+    ref.close()
     sk = socket.socket(); sk.bind(("127.0.0.1", 0)); port = sk.getsockname()[1]; sk.close()
     procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, out)) for r in range(world)]
     for p in procs:
@@ -104,4 +156,8 @@ def test_nccl_slabs_match_single_gpu():
     one._sync_scalars()
     for key in ("dt", "max_div_post", "mean_energy", "max_vorticity"):
         assert abs(out["scalars"][key] - one.scalars[-1][key]) <= 1e-12 * abs(one.scalars[-1][key])
+    for key, exp in (("fixed", pf), ("tol", pt)):
+        got = out["poisson"][key]
+        assert got[1] == exp[1] and got[2] == exp[2] and np.array_equal(got[0], exp[0]), key
+    assert pt[1] == 38
     one.close()

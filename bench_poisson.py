@@ -25,14 +25,74 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 
+def run_slabs(args):
+    """--gpus N > 1: the same red-black solve on x-slabs of n x n cells per GPU (global grid n x (n * N)), one process per
+    GPU: phi halos refreshed over NCCL every 7 iterations (temporally blocked passes in between), the last change
+    all-reduced.  One JSON line per mode, value = global interior cells * sweeps / max-over-ranks device time."""
+    import subprocess
+    if "RANK" not in os.environ:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", "29541", __file__] + sys.argv[1:]
+        return subprocess.call(cmd)
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from bench import measured_peak
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    N = args.n
+    h = 1.0 / (N - 1)
+    cfg = OptimizedTurbulentConfig(nx=N * world, ny=N, memory_efficient=(args.dtype == "f32"), x_min=0.0, x_max=(N * world - 1) * h,
+                                   y_min=0.0, y_max=(N - 1) * h, cylinder_center=((N // 5) * h, (N // 2) * h),
+                                   R_cylinder=(N // 40) * h)
+    s = OptimizedTurbulentSolver(cfg, device=local, nranks=world, rank=rank, setup="device")
+    t = s.device_tensor("phi")
+    g = torch.Generator(device=s.device).manual_seed(1234 + rank)
+    rhs = 0.1 * torch.randn(t.shape, generator=g, dtype=t.dtype, device=s.device)
+    s._phi_exchanger().exchange([rhs])                     # halo columns of the right-hand side = the neighbours' owned values
+    es = 8 if args.dtype == "f64" else 4
+    algo_b = 2 * es + es + 1
+    peak, peak_src = measured_peak()
+    cells = (N - 2) * (N * world - 2)
+    for name, omega in (("rbgs_omega1", 1.0), ("rbsor_omega1.5", 1.5)):
+        s.solve_pressure_slabs(rhs, max_iter=15, tol=0.0, omega=omega)          # warm-up (tensor maps, buffers)
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _, it, last = s.solve_pressure_slabs(rhs, max_iter=args.sweeps, tol=0.0, omega=omega, return_info=True)
+        e1.record()
+        torch.cuda.synchronize(); dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=s.device)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms = float(ms.item())
+        if rank == 0:
+            mlups = cells * it / (ms * 1e-3) / 1e6
+            print(json.dumps({"bench": "poisson", "mode": name, "n_gpus": world, "grid": [N, N * world], "per_gpu": [N, N],
+                              "dtype": args.dtype, "sweeps": it, "ms": ms, "MLUPS": mlups, "scaling": "weak",
+                              "algo_GBs_per_gpu": mlups * 1e6 * algo_b / 1e9 / world,
+                              "frac_of_measured_hbm_peak_per_gpu": mlups * 1e6 * algo_b / 1e9 / world / peak,
+                              "hbm_peak_GBs": peak, "peak_source": peak_src, "last_change": last,
+                              "kernel": "TMA temporally blocked, 7 iterations per NCCL halo refresh",
+                              "halo_bytes_per_refresh_per_gpu": s._phi_exchanger().bytes_per_exchange}), flush=True)
+    s.close()
+    dist.destroy_process_group()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--n", type=int, default=8192)
     ap.add_argument("--sweeps", type=int, default=240)
     ap.add_argument("--dtype", default="f64", choices=["f64", "f32"])
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--depths", default="1,0,2,3,4,6")
     args = ap.parse_args()
+    if args.gpus > 1 or int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        sys.exit(run_slabs(args))
     import numpy as np
     import torch
     from cfd_simulations_b200 import kernels as K

@@ -575,7 +575,8 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
     cudaStream_t s = (cudaStream_t)stream;
     CU(h, cudaSetDevice(h->device));
     const int dtp = h->cfg.dtype;
-    Geom g = make_geom(h->g.ny, h->g.nx, h->g.pitch, dx, dy, h->g.jg0, h->g.nxg);
+    // slabs: max|dphi| is taken over the OWNED columns only (halo columns lose validity between refreshes)
+    Geom g = make_geom(h->g.ny, h->g.nx, h->g.pitch, dx, dy, h->g.jg0, h->g.nxg, h->g.own0, h->g.own1);
     const size_t fb = (size_t)g.ny * g.nx * h->es;
     launch_poisson_reset(h->ctl, s);
     int done_iters = 0, tb_done_iters = -1;

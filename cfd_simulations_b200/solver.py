@@ -310,13 +310,15 @@ class OptimizedTurbulentSolver:
         return (out, it.value, last.value) if return_info else out
 
     # ---- iterative Poisson across x-slabs (halo refresh per pass + all-reduced residual) ----
-    def _poisson_iterations(self, rhs, n, omega):
-        """n plain red-black iterations of solve_pressure_gauss_seidel_fast on the LOCAL array (owned columns + halos),
-        no tolerance stop, no host synchronisation; max|dphi| of the last one stays on the device."""
+    def _poisson_iterations(self, rhs, n, omega, temporal_depth=1):
+        """n red-black iterations of solve_pressure_gauss_seidel_fast on the LOCAL array (owned columns + halos), no
+        tolerance stop, no host synchronisation; max|dphi| of the last one stays on the device.  temporal_depth = 1: one
+        launch pair per iteration (the per-iteration change is observable); 0: the TMA temporally blocked kernel."""
         cfg = self.config
         check(self._lib.b200cfd_poisson(
             self._h, self._d["phi"].data_ptr(), rhs.data_ptr(), self._d["mask"].data_ptr(), cfg.dx, cfg.dy, float(cfg.dt),
-            _lib.POISSON_AS_WRITTEN, int(n), 0.0, float(omega), 1, None, None, _stream_ptr(self.device)), self._h)
+            _lib.POISSON_AS_WRITTEN, int(n), 0.0, float(omega), int(temporal_depth), None, None,
+            _stream_ptr(self.device)), self._h)
 
     def _phi_exchanger(self):
         if self._phi_halo is None and self._nranks > 1:

@@ -63,8 +63,9 @@ def test_local_slabs_poisson_matches_single_slab(nslabs):
     for omega, iters in ((1.0, 23), (1.5, 16), (1.0, 1)):
         p1, it1, l1 = single(iters, 0.0, omega)
         pm, itm, lm = many.solve_pressure(div, iters, 0.0, omega)
-        assert itm == iters and np.array_equal(pm, p1), (omega, iters, rel_l2(pm, p1))
-        assert lm == l1
+        # fixed-count chunks run through the temporally blocked kernel: same iterates up to FMA contraction (1e-15)
+        assert itm == iters and rel_l2(pm, p1) <= 1e-14, (omega, iters, rel_l2(pm, p1))
+        assert abs(lm - l1) <= 1e-12 * l1
     # tolerance mode: a tolerance between the changes of iterations 37 and 38 stops both after exactly 38 iterations
     l37, l38 = single(37, 0.0, 1.0)[2], single(38, 0.0, 1.0)[2]
     assert l38 < l37
@@ -158,6 +159,6 @@ def test_nccl_slabs_match_single_gpu():
         assert abs(out["scalars"][key] - one.scalars[-1][key]) <= 1e-12 * abs(one.scalars[-1][key])
     for key, exp in (("fixed", pf), ("tol", pt)):
         got = out["poisson"][key]
-        assert got[1] == exp[1] and got[2] == exp[2] and np.array_equal(got[0], exp[0]), key
+        assert got[1] == exp[1] and abs(got[2] - exp[2]) <= 1e-12 * exp[2] and rel_l2(got[0], exp[0]) <= 1e-14, key
     assert pt[1] == 38
     one.close()

@@ -481,6 +481,10 @@ int b200cfd_required_halo(const b200cfd_config* cfg, int* left, int* right) {
     const int iters = cfg->clean_iters > 0 ? cfg->clean_iters : 0;
     *left = iters * (cp.apron_h + 3) + 8;
     *right = 3 * iters + 8;
+    // round both up to 16 columns (128 B in fp64): with a slab width that is a multiple of 16 every row of the local
+    // array then starts on a 128-byte boundary (an unaligned pitch costs one extra 32-byte sector per warp access)
+    *left = (*left + 15) / 16 * 16;
+    *right = (*right + 15) / 16 * 16;
     return B200CFD_OK;
 }
 

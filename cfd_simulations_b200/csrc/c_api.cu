@@ -283,7 +283,7 @@ static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, in
             const void* po = it == 0 ? nullptr : h->psi[(it - 1) & 1];
             int pi = 0;
             const bool last_deferred = defer_last_apply && it == iterations - 1;
-            if (out_u && out_v && h->fuse_apply && !last_deferred) {
+            if (out_u && out_v && h->fuse_apply && !h->clean.two_pass && !last_deferred) {
                 // sweep + correction in one kernel, written to the other velocity pair
                 void* uo = (u == h->ua) ? h->ub : h->ua;
                 void* vo = (v == h->va) ? h->vb : h->va;
@@ -294,6 +294,7 @@ static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, in
                 continue;
             }
             launch_clean_sweep(dt, h->g, h->clean, u, v, po, pn, nullptr, nullptr, s);
+            nl += clean_sweep_launches(h->clean) - 1;
             if (in_step) prof_mark(h, it == 0 ? "clean_sweep_1" : "clean_sweep_2", s, pi);
             if (!last_deferred) {
                 launch_clean_apply(dt, h->g, u, v, pn, s); ++nl;

@@ -91,7 +91,7 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
     const int jw0 = js - cp.apron_h;                        // window origin (may be < 1: forced-zero cells)
     const int is = 1 + t * cp.tile_h;
     const int ie = min(is + cp.tile_h, g.ny - 1);
-    const int iw0 = max(1, is - cp.apron_v);
+    const int iw0 = cp.two_pass ? is : max(1, is - cp.apron_v);   // two-pass: own rows only, zero inflow
     const int c0 = jw0 + CPL * lane;
     const int nx = g.nx;
     const double alpha = g.ax * g.dinv;
@@ -141,7 +141,7 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
         }
 #pragma unroll
         for (int m = 0; m < CPL; ++m) {
-            if (!(HAS_OLD && iw0 > 1 && colin[m])) xprev[m] = 0.0;
+            if (!(HAS_OLD && iw0 > 1 && colin[m]) || cp.two_pass) xprev[m] = 0.0;
             if (!HAS_OLD) { pcur[m] = 0.0; pnext[m] = 0.0; }
         }
     }
@@ -253,6 +253,77 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
     }
 }
 
+// Second pass of the two-pass sweep.  The recurrence is linear, so the sweep of a tile from its TRUE inflow row equals
+// its zero-inflow sweep y (first pass, k_clean_sweep with cp.two_pass) plus the homogeneous response c to that row:
+//   c[i,j] = alpha c[i,j-1] + beta c[i-1,j],  c[is-1,:] = psi[is-1,:],  psi[i,j] = y[i,j] + c[i,j].
+// c decays by beta/(1-alpha) per row: after apron_v rows it is below one ulp, so only the first apron_v rows of a tile
+// are touched, and because tile_h > apron_v the inflow row (the LAST row of the tile above) is never one of them — it
+// already holds its final value when this kernel starts.  No u, v, psi_old traffic, no right-hand side: the scan only.
+// Same 128-column windows and horizontal apron as the first pass (c is guessed 0 west of the window).
+template <typename T>
+__global__ void __launch_bounds__(32 * CWARPS)
+k_clean_corr(Geom g, CleanPlan cp, T* __restrict__ psi) {
+    const int lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * CWARPS + (threadIdx.x >> 5);
+    if (tile >= cp.n_strips * (cp.n_tiles - 1)) return;
+    const int s = tile % cp.n_strips, t = 1 + tile / cp.n_strips;
+    const int js = cp.j_first + s * cp.strip_w;
+    const int je = min(js + cp.strip_w, cp.j_end);
+    const int c0 = js - cp.apron_h + CPL * lane;
+    const int is = 1 + t * cp.tile_h;
+    const int ie = min(min(is + cp.tile_h, g.ny - 1), is + cp.apron_v);
+    const int nx = g.nx;
+    const double alpha = g.ax * g.dinv, cn = g.ay * g.dinv;
+    const double a2 = alpha * alpha, a3 = a2 * alpha, a4 = a2 * a2;
+    const double a8 = a4 * a4, a16 = a8 * a8, a32 = a16 * a16, a64 = a32 * a32;
+    bool colin[CPL], own[CPL];
+    double cprev[CPL];
+    const long long rm = (long long)(is - 1) * g.pitch;
+#pragma unroll
+    for (int m = 0; m < CPL; ++m) {
+        const int c = c0 + m, cg = g.jg0 + c;
+        colin[m] = (c >= 1 && c < nx - 1 && cg >= 1 && cg < g.nxg - 1);
+        own[m] = (c >= js && c < je);
+        cprev[m] = colin[m] ? ldg0(psi, rm, c, nx) : 0.0;
+    }
+    double ycur[CPL];
+#pragma unroll
+    for (int m = 0; m < CPL; ++m) ycur[m] = own[m] ? (double)psi[(long long)is * g.pitch + c0 + m] : 0.0;
+    for (int i = is; i < ie; ++i) {
+        const long long ro = (long long)i * g.pitch;
+        double ynext[CPL];
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) ynext[m] = (own[m] && i + 1 < ie) ? (double)psi[ro + g.pitch + c0 + m] : 0.0;
+        double r[CPL];
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) r[m] = colin[m] ? cn * cprev[m] : 0.0;
+        const double t0 = r[0];
+        const double t1 = fma(alpha, t0, r[1]);
+        const double t2 = fma(alpha, t1, r[2]);
+        const double t3 = fma(alpha, t2, r[3]);
+        double B = t3, tmp;
+        tmp = __shfl_up_sync(0xffffffffu, B, 1);  if (lane >= 1)  B = fma(a4, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 2);  if (lane >= 2)  B = fma(a8, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 4);  if (lane >= 4)  B = fma(a16, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 8);  if (lane >= 8)  B = fma(a32, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 16); if (lane >= 16) B = fma(a64, tmp, B);
+        double carry = __shfl_up_sync(0xffffffffu, B, 1);
+        if (lane == 0) carry = 0.0;
+        double x[CPL];
+        x[0] = fma(alpha, carry, t0);
+        x[1] = fma(a2, carry, t1);
+        x[2] = fma(a3, carry, t2);
+        x[3] = fma(a4, carry, t3);
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) {
+            if (!colin[m]) x[m] = 0.0;
+            if (own[m]) psi[ro + c0 + m] = (T)(ycur[m] + x[m]);
+            cprev[m] = x[m];
+            ycur[m] = ynext[m];
+        }
+    }
+}
+
 // u,v[1:-1,1:-1] -= grad(psi)[1:-1,1:-1]   (v5.py:254-256), arithmetic in the field dtype
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -312,6 +383,18 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     if (th > nrows) th = nrows > 0 ? nrows : 1;
     cp.tile_h = th;
     cp.n_tiles = (nrows + th - 1) / th;
+    // two-pass sweep (k_clean_corr): needs tiles taller than the decay length so that a tile's last row is final after the
+    // first pass; worth it when such tiles still fill the machine (otherwise short tiles + re-swept aprons have less latency)
+    cp.two_pass = 0;
+    // OFF by default — measured on B200: parity-green, but no faster (4096x1024: 60.7 + 68.8 us against 56.6 + 71.5 us for
+    // the two sweeps; 16384^2: 1.59 + 1.91 ms against 1.40 + 2.06 ms).  The sweep is bound by the latency of the scan chain
+    // per row at 2 warps per scheduler, and a correction row has the same chain as a full row.
+    if (tune_int("B200CFD_CLEAN_TWO_PASS", 0)) {
+        int th2 = th > Lv + 1 ? th : Lv + 1;
+        if (th2 > nrows) th2 = nrows > 0 ? nrows : 1;
+        const int nt2 = (nrows + th2 - 1) / th2;
+        if (nt2 > 1 && (long long)cp.n_strips * nt2 >= 4ll * n_sm) { cp.two_pass = 1; cp.tile_h = th2; cp.n_tiles = nt2; }
+    }
     return cp;
 }
 
@@ -332,7 +415,7 @@ static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void*
         else launch_pdl(k_clean_sweep<T, false, V, A>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn, uop, vop);      \
     } while (0)
     if (uo && vo) {
-        SWEEP_LAUNCH(0, true);
+        SWEEP_LAUNCH(0, true);                 // (callers only fuse the correction with a one-pass plan)
     } else {
         if (mode == 1) SWEEP_LAUNCH(1, false);
         else if (mode == 2) SWEEP_LAUNCH(2, false);
@@ -349,7 +432,13 @@ void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const voi
     if (nblk <= 0) return;
     if (dtype == 0) launch_clean_sweep_t<double>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
     else launch_clean_sweep_t<float>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
+    if (cp.two_pass && cp.n_tiles > 1) {
+        const int nb2 = (cp.n_strips * (cp.n_tiles - 1) + CWARPS - 1) / CWARPS;
+        if (dtype == 0) k_clean_corr<double><<<nb2, 32 * CWARPS, 0, s>>>(g, cp, (double*)psi_new);
+        else k_clean_corr<float><<<nb2, 32 * CWARPS, 0, s>>>(g, cp, (float*)psi_new);
+    }
 }
+int clean_sweep_launches(const CleanPlan& cp) { return (cp.two_pass && cp.n_tiles > 1) ? 2 : 1; }
 
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s) {
     dim3 grid((g.nx + 63) / 64, (g.ny + 3) / 4), block(64, 4);

@@ -101,11 +101,16 @@ void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, co
                     void* div_out, double inv_dt, StepCtl* ctl, double tol, cudaStream_t s);
 
 // ---- divergence clean-up (lexicographic GS by independent overlapped warp tiles) -----------------
-struct CleanPlan { int strip_w, tile_h, apron_h, apron_v; int n_strips, n_tiles; int j_first, j_end; };
+struct CleanPlan {
+    int strip_w, tile_h, apron_h, apron_v; int n_strips, n_tiles; int j_first, j_end;
+    int two_pass;   // 1: tiles sweep only their own rows from zero inflow, then k_clean_corr adds the homogeneous response
+                    //    to the true inflow over the first apron_v rows of every tile (cleandiv.cu); 0: apron rows re-swept
+};
 CleanPlan clean_plan(const Geom& g, int dtype, int n_sm);
 void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
                         const void* psi_old /*NULL = zeros*/, void* psi_new, void* uo /*NULL = no fused correction*/, void* vo,
                         cudaStream_t s);
+int clean_sweep_launches(const CleanPlan& cp);   // kernels one launch_clean_sweep enqueues (2 with the two-pass plan)
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s);
 
 }  // namespace b200cfd

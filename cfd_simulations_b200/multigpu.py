@@ -179,8 +179,8 @@ class LocalSlabs:
                 b._halo.pack(fb, pb.own0, pb.send_left, b._halo.sbuf_l[k])
                 a._halo.unpack(fa, pa.own1, pa.halo_right, b._halo.sbuf_l[k])
 
-    def solve_pressure(self, div_global, max_iter, tol, omega=1.0):
-        """The slab-decomposed "as written" Poisson solve (solver.solve_pressure_slabs) with the collectives emulated:
+    def solve_pressure(self, div_global, max_iter, tol, omega=1.0, mode="as_written"):
+        """The slab-decomposed Poisson solve (solver.solve_pressure_slabs) with the collectives emulated:
         returns (global phi, iterations, last change)."""
         S = self.slabs
         rhs = []
@@ -188,9 +188,12 @@ class LocalSlabs:
             p = s.plan
             rhs.append(torch.as_tensor(np.ascontiguousarray(div_global[:, p.x_offset:p.x_offset + p.nx_local]),
                                        dtype=s._d["phi"].dtype).to(s.device))
-        it, last = slab_poisson(S, rhs, int(max_iter), float(tol), float(omega),
-                                exchange=lambda: self.refresh_halos(names=("phi",)),
-                                reduce_max=lambda parts: torch.stack(parts).max(dim=0).values)
+        if mode == "jacobi":
+            it, last = slab_jacobi(S, rhs, int(max_iter), exchange=lambda: self.refresh_halos(names=("phi",))), 0.0
+        else:
+            it, last = slab_poisson(S, rhs, int(max_iter), float(tol), float(omega),
+                                    exchange=lambda: self.refresh_halos(names=("phi",)),
+                                    reduce_max=lambda parts: torch.stack(parts).max(dim=0).values)
         return self.gather("phi"), it, last
 
     def set_step(self, step):
@@ -221,6 +224,24 @@ class LocalSlabs:
     def close(self):
         for s in self.slabs:
             s.close()
+
+
+def slab_jacobi(slabs, rhs, sweeps, exchange):
+    """The Jacobi branch of solve_pressure_fast (v5.py:336-346: a fixed number of sweeps, no tolerance) on slabs: the
+    region of validity of the halos shrinks by ONE column per sweep, so they are refreshed once per min(halo) sweeps;
+    the sweeps in between run through the (temporally blocked) Jacobi kernel on the local array."""
+    hl, hr = slabs[0]._halo_req
+    T = max(1, min(hl, hr)) if slabs[0]._nranks > 1 else 64
+    for s in slabs:
+        s._d["phi"].zero_()
+    it = 0
+    while it < sweeps:
+        m = min(T, sweeps - it)
+        for i, s in enumerate(slabs):
+            s._jacobi_sweeps(rhs[i], m)
+        it += m
+        exchange()
+    return it
 
 
 def slab_poisson(slabs, rhs, max_iter, tol, omega, exchange, reduce_max):

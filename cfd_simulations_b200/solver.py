@@ -320,6 +320,13 @@ class OptimizedTurbulentSolver:
             _lib.POISSON_AS_WRITTEN, int(n), 0.0, float(omega), int(temporal_depth), None, None,
             _stream_ptr(self.device)), self._h)
 
+    def _jacobi_sweeps(self, rhs, n):
+        """n sweeps of the Jacobi branch (v5.py:336-346: dx only, 0.25, cfg.dt) on the LOCAL array, no host sync."""
+        cfg = self.config
+        check(self._lib.b200cfd_poisson(
+            self._h, self._d["phi"].data_ptr(), rhs.data_ptr(), self._d["mask"].data_ptr(), cfg.dx, cfg.dy, float(cfg.dt),
+            _lib.POISSON_JACOBI, int(n), 0.0, 1.0, 0, None, None, _stream_ptr(self.device)), self._h)
+
     def _phi_exchanger(self):
         if self._phi_halo is None and self._nranks > 1:
             from . import multigpu
@@ -333,7 +340,7 @@ class OptimizedTurbulentSolver:
                 group=self._group)
         return self._phi_halo
 
-    def solve_pressure_slabs(self, div_u_star, max_iter=None, tol=None, omega=None, return_info=False):
+    def solve_pressure_slabs(self, div_u_star, max_iter=None, tol=None, omega=None, return_info=False, mode="as_written"):
         """solve_pressure_fast / solve_pressure_gauss_seidel_fast "as written" (v5.py:202-226, 328-347) on a grid that is
         slab-decomposed over the ranks.  `div_u_star`: this rank's LOCAL (ny, nx_local) right-hand side, halo columns
         included (`set_global`-style slice of the global array), numpy or CUDA tensor.  Communication-avoiding: the halos
@@ -358,6 +365,13 @@ class OptimizedTurbulentSolver:
                 dist.all_reduce(g, op=dist.ReduceOp.MAX, group=self._group)
             return g
 
+        if mode == "jacobi":       # v5.py:336-346: fixed sweep count, halos refreshed once per min(halo) sweeps
+            it = multigpu.slab_jacobi([self], [rhs], int(cfg.pressure_iterations if max_iter is None else max_iter),
+                                      exchange=(lambda: ex.exchange([t])) if ex is not None else (lambda: None))
+            out = t if isinstance(div_u_star, torch.Tensor) else t.cpu().numpy()
+            return (out, it, 0.0) if return_info else out
+        if mode != "as_written":
+            raise ValueError(f"solve_pressure_slabs: mode {mode!r} (as_written | jacobi)")
         it, last = multigpu.slab_poisson(
             [self], [rhs], int(cfg.pressure_iterations if max_iter is None else max_iter),
             float(cfg.pressure_tolerance if tol is None else tol), float(self._ccfg.omega if omega is None else omega),

@@ -76,6 +76,21 @@ def test_local_slabs_poisson_matches_single_slab(nslabs):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("nslabs", [2, 3])
+def test_local_slabs_jacobi_matches_single_slab(nslabs):
+    """The Jacobi branch (v5.py:336-346) on slabs: halos refreshed once per min(halo) sweeps, same field as one slab."""
+    from cfd_simulations_b200.multigpu import LocalSlabs
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg, div = _poisson_case()
+    one = OptimizedTurbulentSolver(cfg)
+    many = LocalSlabs(cfg, nslabs)
+    for sweeps in (37, 16, 1):
+        p1 = one.solve_pressure_fast(div, mode="jacobi", max_iter=sweeps, temporal_depth=1)
+        pm, itm, _ = many.solve_pressure(div, sweeps, 0.0, mode="jacobi")
+        assert itm == sweeps and rel_l2(pm, p1) <= 1e-14, (sweeps, rel_l2(pm, p1))
+    one.close(); many.close()
+
+
 def test_pack_unpack_columns_roundtrip():
     import ctypes as C
     import torch
@@ -114,10 +129,13 @@ def _nccl_worker(rank, world, port, out):
         phi_fixed = s.gather("phi")
         _, itt, lt = s.solve_pressure_slabs(loc, max_iter=5000, tol=float(out["tol"]), omega=1.0, return_info=True)
         phi_tol = s.gather("phi")
+        _, itj, _ = s.solve_pressure_slabs(loc, max_iter=37, return_info=True, mode="jacobi")
+        phi_jac = s.gather("phi")
         if rank == 0:
             out["fields"] = res
             out["scalars"] = s.scalars[-1]
             out["poisson"] = {"fixed": (phi_fixed, itf, lf), "tol": (phi_tol, itt, lt)}
+            out["jacobi"] = (phi_jac, itj)
         s.close()
     finally:
         dist.destroy_process_group()
@@ -141,6 +159,7 @@ def test_nccl_slabs_match_single_gpu():
     pf = single(23, 0.0)
     pt = single(5000, float(out["tol"]))
     pf, pt = (pf[0].copy(), pf[1], pf[2]), (pt[0].copy(), pt[1], pt[2])
+    pj = ref.solve_pressure_fast(div, mode="jacobi", max_iter=37, temporal_depth=1).copy()
     ref.close()
     sk = socket.socket(); sk.bind(("127.0.0.1", 0)); port = sk.getsockname()[1]; sk.close()
     procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, out)) for r in range(world)]
@@ -161,4 +180,5 @@ def test_nccl_slabs_match_single_gpu():
         got = out["poisson"][key]
         assert got[1] == exp[1] and abs(got[2] - exp[2]) <= 1e-12 * exp[2] and rel_l2(got[0], exp[0]) <= 1e-14, key
     assert pt[1] == 38
+    assert out["jacobi"][1] == 37 and rel_l2(out["jacobi"][0], pj) <= 1e-14
     one.close()

@@ -253,6 +253,162 @@ k_clean_sweep(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict
     }
 }
 
+// Lean form of the one-pass sweep for grids whose row length is a multiple of 4 (every shipped configuration).  Same
+// arithmetic, same order, bit-identical results; what changes is the instruction count per row (ncu, r01f: 369 SASS
+// instructions per row of which 64 were fp64 math or shuffles — the rest were per-element bounds tests, 64-bit address
+// arithmetic, zero fills and register rotation):
+//   * the window origin and nx are multiples of 4, so a lane's four columns are all inside [0, nx) or all outside: the
+//     lane's base column is CLAMPED into the row once, every load is an unguarded 128-bit access off a row pointer that
+//     advances by the pitch.  A clamped lane reads finite garbage, but all of its columns are non-updated (colin false:
+//     r and x are selected to 0, never multiplied), and the only in-range columns that see it are c = 0 and c = nx-1,
+//     which are non-updated themselves;
+//   * on the last row the look-ahead pointers stay where they are (a re-read that hits L1) instead of zero-filling;
+//   * the row loop is unrolled by 6 = lcm(3 rows of v, 2 rows of psi_old in flight): the rotation is register renaming.
+template <typename T> struct Ld4;
+template <> struct Ld4<double> {
+    static __device__ __forceinline__ void ld(const double* __restrict__ p, double (&o)[CPL]) {
+        const double2 a = __ldg(reinterpret_cast<const double2*>(p)), b = __ldg(reinterpret_cast<const double2*>(p + 2));
+        o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+    }
+};
+template <> struct Ld4<float> {
+    static __device__ __forceinline__ void ld(const float* __restrict__ p, double (&o)[CPL]) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(p));
+        o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+    }
+};
+
+template <typename T, bool HAS_OLD, int UNR>
+__global__ void __launch_bounds__(32 * CWARPS)
+k_clean_sweep_lean(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ pold,
+                   T* __restrict__ pnew) {
+    pdl_wait(); pdl_trigger();
+    const int lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * CWARPS + (threadIdx.x >> 5);
+    if (tile >= cp.n_strips * cp.n_tiles) return;          // whole warp exits together
+    const int s = tile % cp.n_strips, t = tile / cp.n_strips;
+    const int js = cp.j_first + s * cp.strip_w;
+    const int je = min(js + cp.strip_w, cp.j_end);
+    const int is = 1 + t * cp.tile_h;
+    const int ie = min(is + cp.tile_h, g.ny - 1);
+    const int iw0 = max(1, is - cp.apron_v);
+    const int iend = ie - 1;
+    const int nx = g.nx;
+    const int c0 = js - cp.apron_h + CPL * lane;            // true first column of the lane (multiple of 4)
+    const int c0c = min(max(c0, 0), nx - CPL);              // clamped: where the lane loads from
+    const long long pitch = g.pitch;
+    const double alpha = g.ax * g.dinv;
+    const double a2 = alpha * alpha, a3 = a2 * alpha, a4 = a2 * a2;
+    const double a8 = a4 * a4, a16 = a8 * a8, a32 = a16 * a16, a64 = a32 * a32;
+    const double ce = g.ax * g.dinv, cn = g.ay * g.dinv;
+    const double hdx = g.hdx, hdy = g.hdy, dinv = g.dinv;
+
+    bool colin[CPL], stm[CPL];
+#pragma unroll
+    for (int m = 0; m < CPL; ++m) {
+        const int c = c0 + m, cg = g.jg0 + c;
+        colin[m] = (c >= 1 && c < nx - 1 && cg >= 1 && cg < g.nxg - 1);
+        stm[m] = (c >= js && c < je);
+    }
+    const bool st_all = (c0 >= js && c0 + CPL <= je);
+
+    double xprev[CPL], v_im1[CPL], v_i[CPL], pcur[CPL], ucur[CPL], vnext[CPL], pnext[CPL];
+    const T* qv = v + (long long)(iw0 - 1) * pitch + c0c;
+    const T* qu = u + (long long)iw0 * pitch + c0c;
+    const T* qp = HAS_OLD ? pold + (long long)(iw0 - 1) * pitch + c0c : nullptr;
+    Ld4<T>::ld(qv, v_im1);
+    Ld4<T>::ld(qv + pitch, v_i);
+    Ld4<T>::ld(qv + 2 * pitch, vnext);
+    Ld4<T>::ld(qu, ucur);
+    if (HAS_OLD) {
+        Ld4<T>::ld(qp, xprev);
+        Ld4<T>::ld(qp + pitch, pcur);
+        Ld4<T>::ld(qp + 2 * pitch, pnext);
+    }
+#pragma unroll
+    for (int m = 0; m < CPL; ++m) {
+        if (!(HAS_OLD && iw0 > 1 && colin[m])) xprev[m] = 0.0;
+        if (!HAS_OLD) { pcur[m] = 0.0; pnext[m] = 0.0; }
+    }
+    // look-ahead pointers: u row min(i+1, iend), v and psi_old row min(i+2, iend+1)  (iend + 1 <= ny - 1)
+    {
+        const long long du = (iw0 + 1 <= iend) ? 1 : 0;
+        qu += du * pitch;
+        qv += (2 + du) * pitch;
+        if (HAS_OLD) qp += (2 + du) * pitch;
+    }
+    T* qn = pnew + (long long)iw0 * pitch + c0;             // dereferenced only where stm[] holds
+
+#pragma unroll UNR
+    for (int i = iw0; i <= iend; ++i) {
+        double un_[CPL], vn2[CPL], pn2[CPL];
+        Ld4<T>::ld(qu, un_);
+        Ld4<T>::ld(qv, vn2);
+        if (HAS_OLD) Ld4<T>::ld(qp, pn2);
+        if (i + CPFD < ie) {
+            prefetch_l2(qu + (CPFD - 1) * pitch);
+            prefetch_l2(qv + (CPFD - 1) * pitch);
+            if (HAS_OLD) prefetch_l2(qp + (CPFD - 1) * pitch);
+        }
+        {
+            const long long adv = (i + 2 <= iend) ? pitch : 0;
+            qu += adv; qv += adv;
+            if (HAS_OLD) qp += adv;
+        }
+        // ---- right-hand side of row i
+        const double uE3 = __shfl_down_sync(0xffffffffu, ucur[0], 1);
+        const double uW0 = __shfl_up_sync(0xffffffffu, ucur[CPL - 1], 1);
+        const double pE3 = HAS_OLD ? __shfl_down_sync(0xffffffffu, pcur[0], 1) : 0.0;
+        double r[CPL], x[CPL];
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) {
+            const double uE = (m < CPL - 1) ? ucur[(m + 1) % CPL] : (lane < 31 ? uE3 : 0.0);
+            const double uW = (m > 0) ? ucur[(m + CPL - 1) % CPL] : (lane > 0 ? uW0 : 0.0);
+            const double D = Rnd<T>::r((uE - uW) * hdx + (vnext[m] - v_im1[m]) * hdy);
+            const double pE = (m < CPL - 1) ? pcur[(m + 1) % CPL] : (lane < 31 ? pE3 : 0.0);
+            const double rr = ce * pE + cn * (pnext[m] + xprev[m]) - D * dinv;
+            r[m] = colin[m] ? rr : 0.0;
+        }
+        // ---- west recurrence x[c] = alpha x[c-1] + r[c]: serial in the lane, Kogge-Stone across lanes
+        const double t0 = r[0];
+        const double t1 = fma(alpha, t0, r[1]);
+        const double t2 = fma(alpha, t1, r[2]);
+        const double t3 = fma(alpha, t2, r[3]);
+        double B = t3, tmp;
+        tmp = __shfl_up_sync(0xffffffffu, B, 1);  if (lane >= 1)  B = fma(a4, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 2);  if (lane >= 2)  B = fma(a8, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 4);  if (lane >= 4)  B = fma(a16, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 8);  if (lane >= 8)  B = fma(a32, tmp, B);
+        tmp = __shfl_up_sync(0xffffffffu, B, 16); if (lane >= 16) B = fma(a64, tmp, B);
+        double carry = __shfl_up_sync(0xffffffffu, B, 1);
+        if (lane == 0) carry = 0.0;
+        x[0] = Rnd<T>::r(fma(alpha, carry, t0));
+        x[1] = Rnd<T>::r(fma(a2, carry, t1));
+        x[2] = Rnd<T>::r(fma(a3, carry, t2));
+        x[3] = Rnd<T>::r(fma(a4, carry, t3));
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) if (!colin[m]) x[m] = 0.0;
+        // ---- store owned cells
+        if (i >= is) {
+            if (st_all) {
+                Row4<T, 2>::st(qn, 0, x);
+            } else {
+#pragma unroll
+                for (int m = 0; m < CPL; ++m) if (stm[m]) qn[m] = (T)x[m];
+            }
+        }
+        qn += pitch;
+        // ---- rotate
+#pragma unroll
+        for (int m = 0; m < CPL; ++m) {
+            xprev[m] = x[m];
+            v_im1[m] = v_i[m]; v_i[m] = vnext[m]; vnext[m] = vn2[m];
+            if (HAS_OLD) { pcur[m] = pnext[m]; pnext[m] = pn2[m]; }     // (no psi_old: both stay 0)
+            ucur[m] = un_[m];
+        }
+    }
+}
+
 // Second pass of the two-pass sweep.  The recurrence is linear, so the sweep of a tile from its TRUE inflow row equals
 // its zero-inflow sweep y (first pass, k_clean_sweep with cp.two_pass) plus the homogeneous response c to that row:
 //   c[i,j] = alpha c[i,j-1] + beta c[i-1,j],  c[is-1,:] = psi[is-1,:],  psi[i,j] = y[i,j] + c[i,j].
@@ -414,8 +570,23 @@ static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void*
         if (po) launch_pdl(k_clean_sweep<T, true, V, A>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, po, pn, uop, vop);         \
         else launch_pdl(k_clean_sweep<T, false, V, A>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn, uop, vop);      \
     } while (0)
+    // lean kernel (default): one-pass plan, 4-aligned rows of a length that is a multiple of 4; B200CFD_CLEAN_LEAN=0
+    // falls back to the general kernel (which also serves every other shape)
+    static const int lean_on = tune_int("B200CFD_CLEAN_LEAN", 1);
     if (uo && vo) {
         SWEEP_LAUNCH(0, true);                 // (callers only fuse the correction with a one-pass plan)
+    } else if (lean_on && vec && !cp.two_pass && g.nx % 4 == 0 && g.nx >= 4) {
+        static const int unr = tune_int("B200CFD_CLEAN_UNROLL", 6);    // developer knob: 1, 2, 3 or 6 rows per loop trip
+#define LEAN_LAUNCH(U)                                                                                              \
+    do {                                                                                                            \
+        if (po) launch_pdl(k_clean_sweep_lean<T, true, U>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, po, pn); \
+        else launch_pdl(k_clean_sweep_lean<T, false, U>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn); \
+    } while (0)
+        if (unr == 1) LEAN_LAUNCH(1);
+        else if (unr == 2) LEAN_LAUNCH(2);
+        else if (unr == 3) LEAN_LAUNCH(3);
+        else LEAN_LAUNCH(6);
+#undef LEAN_LAUNCH
     } else {
         if (mode == 1) SWEEP_LAUNCH(1, false);
         else if (mode == 2) SWEEP_LAUNCH(2, false);

@@ -278,8 +278,8 @@ template <> struct Ld4<float> {
     }
 };
 
-template <typename T, bool HAS_OLD, int UNR>
-__global__ void __launch_bounds__(32 * CWARPS)
+template <typename T, bool HAS_OLD, int UNR, int MINB>
+__global__ void __launch_bounds__(32 * CWARPS, MINB)
 k_clean_sweep_lean(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __restrict__ v, const T* __restrict__ pold,
                    T* __restrict__ pnew) {
     pdl_wait(); pdl_trigger();
@@ -302,6 +302,8 @@ k_clean_sweep_lean(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __res
     const double a8 = a4 * a4, a16 = a8 * a8, a32 = a16 * a16, a64 = a32 * a32;
     const double ce = g.ax * g.dinv, cn = g.ay * g.dinv;
     const double hdx = g.hdx, hdy = g.hdy, dinv = g.dinv;
+    const int pfd = cp.pfd;
+    const long long pfo = (long long)(pfd - 1) * pitch;
 
     bool colin[CPL], stm[CPL];
 #pragma unroll
@@ -345,10 +347,10 @@ k_clean_sweep_lean(Geom g, CleanPlan cp, const T* __restrict__ u, const T* __res
         Ld4<T>::ld(qu, un_);
         Ld4<T>::ld(qv, vn2);
         if (HAS_OLD) Ld4<T>::ld(qp, pn2);
-        if (i + CPFD < ie) {
-            prefetch_l2(qu + (CPFD - 1) * pitch);
-            prefetch_l2(qv + (CPFD - 1) * pitch);
-            if (HAS_OLD) prefetch_l2(qp + (CPFD - 1) * pitch);
+        if (i + pfd < ie) {
+            prefetch_l2(qu + pfo);
+            prefetch_l2(qv + pfo);
+            if (HAS_OLD) prefetch_l2(qp + pfo);
         }
         {
             const long long adv = (i + 2 <= iend) ? pitch : 0;
@@ -542,6 +544,8 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     // two-pass sweep (k_clean_corr): needs tiles taller than the decay length so that a tile's last row is final after the
     // first pass; worth it when such tiles still fill the machine (otherwise short tiles + re-swept aprons have less latency)
     cp.two_pass = 0;
+    cp.pfd = tune_int("B200CFD_CLEAN_PFD", CPFD);
+    if (cp.pfd < 1) cp.pfd = 1;
     // OFF by default — measured on B200: parity-green, but no faster (4096x1024: 60.7 + 68.8 us against 56.6 + 71.5 us for
     // the two sweeps; 16384^2: 1.59 + 1.91 ms against 1.40 + 2.06 ms).  The sweep is bound by the latency of the scan chain
     // per row at 2 warps per scheduler, and a correction row has the same chain as a full row.
@@ -576,16 +580,15 @@ static void launch_clean_sweep_t(const Geom& g, const CleanPlan& cp, const void*
     if (uo && vo) {
         SWEEP_LAUNCH(0, true);                 // (callers only fuse the correction with a one-pass plan)
     } else if (lean_on && vec && !cp.two_pass && g.nx % 4 == 0 && g.nx >= 4) {
-        static const int unr = tune_int("B200CFD_CLEAN_UNROLL", 6);    // developer knob: 1, 2, 3 or 6 rows per loop trip
-#define LEAN_LAUNCH(U)                                                                                              \
+        static const int unr = tune_int("B200CFD_CLEAN_UNROLL", 6);    // developer knobs: 2 or 6 rows per loop trip,
+        static const int minb = tune_int("B200CFD_CLEAN_MINB", 3);     // 3 or 4 resident blocks per SM (register cap)
+#define LEAN_LAUNCH(U, B)                                                                                           \
     do {                                                                                                            \
-        if (po) launch_pdl(k_clean_sweep_lean<T, true, U>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, po, pn); \
-        else launch_pdl(k_clean_sweep_lean<T, false, U>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn); \
+        if (po) launch_pdl(k_clean_sweep_lean<T, true, U, B>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, po, pn); \
+        else launch_pdl(k_clean_sweep_lean<T, false, U, B>, dim3(nblk), dim3(32 * CWARPS), s, g, cp, up, vp, (const T*)nullptr, pn); \
     } while (0)
-        if (unr == 1) LEAN_LAUNCH(1);
-        else if (unr == 2) LEAN_LAUNCH(2);
-        else if (unr == 3) LEAN_LAUNCH(3);
-        else LEAN_LAUNCH(6);
+        if (unr == 2) { if (minb == 4) LEAN_LAUNCH(2, 4); else LEAN_LAUNCH(2, 3); }
+        else { if (minb == 4) LEAN_LAUNCH(6, 4); else LEAN_LAUNCH(6, 3); }
 #undef LEAN_LAUNCH
     } else {
         if (mode == 1) SWEEP_LAUNCH(1, false);

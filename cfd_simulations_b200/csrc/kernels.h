@@ -103,6 +103,7 @@ void launch_div_rb1(int dtype, const Geom& g, const void* us, const void* vs, co
 // ---- divergence clean-up (lexicographic GS by independent overlapped warp tiles) -----------------
 struct CleanPlan {
     int strip_w, tile_h, apron_h, apron_v; int n_strips, n_tiles; int j_first, j_end;
+    int pfd;        // L2 prefetch distance of the lean sweep, rows
     int two_pass;   // 1: tiles sweep only their own rows from zero inflow, then k_clean_corr adds the homogeneous response
                     //    to the true inflow over the first apron_v rows of every tile (cleandiv.cu); 0: apron rows re-swept
 };

@@ -43,6 +43,7 @@ struct b200cfd_handle {
     bool fast = false;                // row-marching fast kernels applicable (decided when the fields are bound)
     bool fuse_apply = false;          // clean sweep writes the corrected velocity itself: parity-green but measured SLOWER on B200 (the sweep is issue-bound), off unless B200CFD_FUSE_APPLY is set
     bool fuse_k23 = true;             // K2 + K3 in one kernel on the fast path (B200CFD_NO_FUSE_K23 turns it off)
+    bool fuse_corr = true;            // 2 clean iterations on the fast path: the second sweep applies the first correction on its load side and finalize applies both (no k_clean_apply pass); B200CFD_FUSE_CORR=0 turns it off
     // caller-owned (bound) device memory
     void *u = nullptr, *v = nullptr, *phi = nullptr, *us = nullptr, *vs = nullptr, *div = nullptr, *tau = nullptr, *nu_t = nullptr;
     const double* ibm = nullptr;
@@ -55,6 +56,7 @@ struct b200cfd_handle {
     cudaGraphExec_t step_graph = nullptr;
     cudaGraphExec_t begin_graph = nullptr;   // the step without its closing kernel (multi-GPU: all_gather in between)
     PoissonTB* tb = nullptr;          // temporally blocked Poisson state (tensor maps, scratch)
+    bool last_poisson_tb = false;     // the last b200cfd_poisson call ran through the temporally blocked kernel
     int gpu_launches = 0;             // kernels enqueued by the last b200cfd_step call (per step)
     // optional per-phase profiling (CUDA events between the kernels of a step; non-graph path only)
     bool profiling = false;
@@ -191,6 +193,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
         h->fast = h->cfg.use_supg && !h->cfg.use_les && fast_path_ok(h->g, ptrs, 11) && !getenv("B200CFD_NO_FAST");
         h->fuse_k23 = !getenv("B200CFD_NO_FUSE_K23");
         h->fuse_apply = getenv("B200CFD_FUSE_APPLY") != nullptr;
+        { const char* e = getenv("B200CFD_FUSE_CORR"); h->fuse_corr = !(e && *e == '0'); }
         CU(h, cudaSetDevice(h->device));
         launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
         CU(h, cudaDeviceSynchronize());
@@ -260,11 +263,30 @@ static int enqueue_step_poisson(b200cfd_handle* h, cudaStream_t s) {
 static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& idx);
 // out_u / out_v (in-step fast path only): where the velocity that still needs the deferred last correction lives
 static int enqueue_clean(b200cfd_handle* h, void* u, void* v, int iterations, int mode, cudaStream_t s, void** last_psi, bool in_step = false,
-                         bool defer_last_apply = false, void** out_u = nullptr, void** out_v = nullptr) {
+                         bool defer_last_apply = false, void** out_u = nullptr, void** out_v = nullptr, void** first_psi = nullptr) {
     const int dt = h->cfg.dtype;
     const size_t fb = (size_t)h->cfg.ny * h->cfg.nx * h->es;
     int nl = 0;
     void* last = nullptr;
+    if (first_psi) *first_psi = nullptr;
+    if (mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && in_step && defer_last_apply && first_psi && iterations == 2 && h->fuse_corr &&
+        clean_sweep_tma_ok(dt, h->g, h->clean, u, v, h->psi[0], h->psi[1])) {
+        // both corrections deferred: sweep 1 (psi_old = 0) -> psi[0]; sweep 2 streams psi[0] as psi_old AND applies
+        // u,v -= grad(psi[0]) on its load side -> psi[1]; the finalize kernel applies both to the stored u, v
+        int pi = 0;
+        if (launch_clean_sweep_tma(dt, h->g, h->clean, u, v, nullptr, h->psi[0], 0, s)) {
+            prof_mark(h, "clean_sweep_1", s, pi);
+            if (launch_clean_sweep_tma(dt, h->g, h->clean, u, v, h->psi[0], h->psi[1], 2, s)) {
+                prof_mark(h, "clean_sweep_2", s, pi);
+                *first_psi = h->psi[0];
+                if (last_psi) *last_psi = h->psi[1];
+                if (out_u) *out_u = u;
+                if (out_v) *out_v = v;
+                return 2;
+            }
+        }
+        cudaGetLastError();   // a failed launch falls through to the unfused path below, which redoes both sweeps
+    }
     if (mode == B200CFD_CLEANDIV_REDBLACK) {
         // NOT reference parity: same update, red-black ordering, in place on psi[0] (inv_dt = -1 turns
         // the Poisson colour kernel's "+ div/dt" into "- div")
@@ -349,14 +371,15 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     }
     // fast path: the last clean-divergence correction u,v -= grad(psi) is applied on the fly by the finalize kernel
     const bool defer = h->fast && c.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && c.clean_iters > 0;
-    void* last_psi = nullptr;
+    void *last_psi = nullptr, *first_psi = nullptr;
     void *fu = h->ua, *fv = h->va;   // velocity entering the finalize kernel
-    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer, defer ? &fu : nullptr, defer ? &fv : nullptr);
+    nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer, defer ? &fu : nullptr, defer ? &fv : nullptr,
+                        defer ? &first_psi : nullptr);
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
-    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
+    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, defer ? first_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
     else launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s);
     ++nl;
-    prof_mark(h, "finalize", s, pi);
+    prof_mark(h, (defer && first_psi) ? "finalize2" : "finalize", s, pi);
     if (close) launch_ctl_reduce_end(h->ctl, h->cp, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->nut_part, h->ring, h->ring_cap, s);
     else launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->nut_part, s);
     ++nl;
@@ -584,6 +607,7 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
     Geom g = make_geom(h->g.ny, h->g.nx, h->g.pitch, dx, dy, h->g.jg0, h->g.nxg, h->g.own0, h->g.own1);
     const size_t fb = (size_t)g.ny * g.nx * h->es;
     launch_poisson_reset(h->ctl, s);
+    h->last_poisson_tb = false;
     int done_iters = 0, tb_done_iters = -1;
     double tb_last_change = 0.0;
     if (mode == B200CFD_POISSON_JACOBI) {
@@ -592,6 +616,7 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
         if (temporal_depth != 1 && max_iter >= 2) {
             int rc = poisson_tb_jacobi(&h->tb, dtp, g, h->n_sm, phi, rhs_div, mask, k, max_iter, temporal_depth, &it, s);
             if (rc < 0) return fail(h, B200CFD_ECUDA, "temporally blocked Jacobi: %s", poisson_tb_error());
+            h->last_poisson_tb = it > 0;
         }
         if (it < max_iter) {
             int rc = ensure_tmp(h); if (rc) return rc;
@@ -639,6 +664,7 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
                                       check ? tol : 0.0, &tb_last);
             if (rc < 0) return fail(h, B200CFD_ECUDA, "temporally blocked red-black: %s", poisson_tb_error());
             tb_ran = it > 0;
+            h->last_poisson_tb = tb_ran;
         }
         const int chunk = 32;
         while (!tb_ran && it < iters) {
@@ -673,6 +699,17 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
         if (iters_done) *iters_done = counted ? c.pois_iters : done_iters;
         if (last_change) *last_change = c.pois_last;
     }
+    return B200CFD_OK;
+}
+
+// What the last b200cfd_poisson call did: out4 = {temporal depth used (1 = one-sweep kernels), HBM passes of the
+// temporally blocked kernel (0 when it did not run), bytes per cell per pass of that kernel, reserved}.
+int b200cfd_poisson_info(b200cfd_handle* h, int* out4) {
+    if (!h || !out4) return B200CFD_EINVAL;
+    int depth = 0, passes = 0;
+    poisson_tb_info(h->tb, &depth, &passes);
+    const bool tb = h->last_poisson_tb;
+    out4[0] = tb ? depth : 1; out4[1] = tb ? passes : 0; out4[2] = 3 * h->es; out4[3] = 0;
     return B200CFD_OK;
 }
 

@@ -604,6 +604,8 @@ void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const voi
     const int ntile = cp.n_strips * cp.n_tiles;
     const int nblk = (ntile + CWARPS - 1) / CWARPS;
     if (nblk <= 0) return;
+    // default: rows staged by TMA (cleandiv_tma.cu); falls through to the register-marching kernels when not applicable
+    if (!uo && !vo && launch_clean_sweep_tma(dtype, g, cp, u, v, psi_old, psi_new, psi_old ? 1 : 0, s)) return;
     if (dtype == 0) launch_clean_sweep_t<double>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
     else launch_clean_sweep_t<float>(g, cp, u, v, psi_old, psi_new, uo, vo, nblk, s);
     if (cp.two_pass && cp.n_tiles > 1) {

@@ -82,7 +82,7 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
                                  int n_sm, cudaStream_t s);
 int finalize_fast_num_partials(const Geom& g, int n_sm);
 void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
-                          const void* psi_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,
+                          const void* psi_or_null, const void* psi1_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,
                           const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
                           int n_sm, cudaStream_t s);
 void launch_rb1_close(StepCtl* ctl, double tol, cudaStream_t s);
@@ -111,6 +111,12 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm);
 void launch_clean_sweep(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v,
                         const void* psi_old /*NULL = zeros*/, void* psi_new, void* uo /*NULL = no fused correction*/, void* vo,
                         cudaStream_t s);
+// the same sweep with its rows staged in shared memory by TMA (cleandiv_tma.cu).  mode 0: psi_old = 0; 1: psi_old streamed;
+// 2: psi_old = psi_1 streamed and the correction u,v -= grad(psi_1) applied on the load side.  false = not applicable / failed
+bool clean_sweep_tma_ok(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v, const void* psi_old,
+                        const void* psi_new);
+bool launch_clean_sweep_tma(int dtype, const Geom& g, const CleanPlan& cp, const void* u, const void* v, const void* psi_old,
+                            void* psi_new, int mode, cudaStream_t s);
 int clean_sweep_launches(const CleanPlan& cp);   // kernels one launch_clean_sweep enqueues (2 with the two-pass plan)
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s);
 

@@ -34,7 +34,13 @@ struct PoissonTB {
     void* alt = nullptr;        // ping-pong partner of phi
     size_t bytes = 0;
     unsigned long long* slots = nullptr;   // per-iteration max|dphi| of the last pass (TB_MAX_DEPTH entries)
+    int last_depth = 0, last_passes = 0;   // what the last solve did (b200cfd_poisson_info)
 };
+
+void poisson_tb_info(const PoissonTB* tb, int* depth, int* passes) {
+    *depth = tb ? tb->last_depth : 0;
+    *passes = tb ? tb->last_passes : 0;
+}
 
 void poisson_tb_destroy(PoissonTB* tb) {
     if (!tb) return;
@@ -281,8 +287,10 @@ static int tb_run(PoissonTB** ptb, int dtype, int mode, const Geom& g, void* phi
     void* cur = phi; void* nxt = tb->alt;
     int done = 0;
     const bool check = tol > 0.0 && mode == 1;
+    tb->last_depth = depth; tb->last_passes = 0;
     auto pass = [&](int d) -> int {
         P.depth = d;
+        ++tb->last_passes;
         const CUtensorMap& mc = cur == phi ? m_phi : m_alt;
         unsigned long long* sl = check ? tb->slots : nullptr;
         if (check && cudaMemsetAsync(tb->slots, 0, TB_MAX_DEPTH * sizeof(unsigned long long), s) != cudaSuccess) return -1;

@@ -8,6 +8,7 @@ namespace b200cfd {
 struct PoissonTB;
 const char* poisson_tb_error();
 void poisson_tb_destroy(PoissonTB* tb);
+void poisson_tb_info(const PoissonTB* tb, int* depth, int* passes);   // depth and HBM passes of the last solve
 // returns 0 on success (possibly with *iters_done == 0 when the shape is not supported), < 0 on CUDA errors
 int poisson_tb_jacobi(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
                       double dx2_over_dt, int sweeps, int depth, int* iters_done, cudaStream_t s);

@@ -335,12 +335,18 @@ template <typename T> __device__ __forceinline__ D2 ld2g(const T* __restrict__ p
 __device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 __device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
 
-template <typename T, bool PSI>
+// one row of the clean-divergence potentials a lane holds: p = the LAST iteration's psi, q = the first iteration's psi_1
+// (NPSI == 2: both corrections are pending, the sweep of the second iteration applied the first one only on its load side)
+struct PsiRow { D2 p, q; };
+
+template <typename T, int NPSI>
 __global__ void __launch_bounds__(FBT, 3)
 k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
-                const T* __restrict__ psi, T* __restrict__ u, T* __restrict__ v, const double* __restrict__ ibm,
-                const uint8_t* __restrict__ mask, const double* __restrict__ y, double* __restrict__ ke_part,
-                unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+                const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u, T* __restrict__ v,
+                const double* __restrict__ ibm, const uint8_t* __restrict__ mask, const double* __restrict__ y,
+                double* __restrict__ ke_part, unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags,
+                int ntx, int rpb) {
+    constexpr bool PSI = NPSI > 0;
     pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
@@ -371,20 +377,38 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
             const long long kk = (long long)(g.ny - 1) * g.pitch + c0;
             st2<T>(u, kk, 0.0, 0.0); st2<T>(v, kk, 0.0, 0.0); acc.cnt += (ownx ? 1 : 0) + (owny ? 1 : 0);
         }
-        // velocity of one row after the pending correction, from its stored values and three psi rows (all lanes:
-        // the x-neighbours of psi come from shuffles)
-        auto apply_row = [&](int row, const D2& ur, const D2& vr, const D2& pS, const D2& pC, const D2& pN, D2& fu, D2& fv) {
+        const PsiRow PZ = {{0, 0}, {0, 0}};
+        auto ldpsi = [&](long long row_off) {
+            PsiRow r = PZ;
+            if (PSI) r.p = ld2g<T>(psi, row_off, c0, inb);
+            if (NPSI == 2) r.q = ld2g<T>(psi1, row_off, c0, inb);
+            return r;
+        };
+        // velocity of one row after the pending correction(s), from its stored values and three psi rows (all lanes:
+        // the x-neighbours of psi come from shuffles).  NPSI == 2: first u,v -= grad(psi_1), then -= grad(psi): the two
+        // roundings of the reference's two in-place updates (v5.py:254-256, executed twice).
+        auto apply_row = [&](int row, const D2& ur, const D2& vr, const PsiRow& pS, const PsiRow& pC, const PsiRow& pN, D2& fu, D2& fv) {
             fu = ur; fv = vr;
             if (PSI) {
-                const double pW = shfl_up1(pC.y), pE = shfl_dn1(pC.x);
+                const double pW = shfl_up1(pC.p.y), pE = shfl_dn1(pC.p.x);
+                double qW = 0.0, qE = 0.0;
+                if (NPSI == 2) { qW = shfl_up1(pC.q.y); qE = shfl_dn1(pC.q.x); }
                 if (row >= 1 && row < g.ny - 1) {
                     if (inx) {
-                        fu.x = Rnd<T>::r(ur.x - Rnd<T>::r((pC.y - pW) * g.hdx));
-                        fv.x = Rnd<T>::r(vr.x - Rnd<T>::r((pN.x - pS.x) * g.hdy));
+                        if (NPSI == 2) {
+                            fu.x = Rnd<T>::r(fu.x - Rnd<T>::r((pC.q.y - qW) * g.hdx));
+                            fv.x = Rnd<T>::r(fv.x - Rnd<T>::r((pN.q.x - pS.q.x) * g.hdy));
+                        }
+                        fu.x = Rnd<T>::r(fu.x - Rnd<T>::r((pC.p.y - pW) * g.hdx));
+                        fv.x = Rnd<T>::r(fv.x - Rnd<T>::r((pN.p.x - pS.p.x) * g.hdy));
                     }
                     if (iny) {
-                        fu.y = Rnd<T>::r(ur.y - Rnd<T>::r((pE - pC.x) * g.hdx));
-                        fv.y = Rnd<T>::r(vr.y - Rnd<T>::r((pN.y - pS.y) * g.hdy));
+                        if (NPSI == 2) {
+                            fu.y = Rnd<T>::r(fu.y - Rnd<T>::r((qE - pC.q.x) * g.hdx));
+                            fv.y = Rnd<T>::r(fv.y - Rnd<T>::r((pN.q.y - pS.q.y) * g.hdy));
+                        }
+                        fu.y = Rnd<T>::r(fu.y - Rnd<T>::r((pE - pC.p.x) * g.hdx));
+                        fv.y = Rnd<T>::r(fv.y - Rnd<T>::r((pN.p.y - pS.p.y) * g.hdy));
                     }
                 }
             }
@@ -401,15 +425,16 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
         };
         if (lo < hi) {
             long long ro = (long long)lo * g.pitch;
-            D2 pm = {0, 0}, pc = {0, 0}, pn = {0, 0};     // psi rows (i), (i+1), (i+2) while row i is processed
+            PsiRow pm = PZ, pc = PZ, pn = PZ;             // psi rows (i), (i+1), (i+2) while row i is processed
             D2 gum = {0, 0}, fvm, fuc, fvc, mc;
             {   // rows lo-1 and lo
-                D2 pmm = {0, 0}, fum;
+                PsiRow pmm = PZ;
+                D2 fum;
                 if (PSI) {
-                    if (lo - 2 >= 0) pmm = ld2g<T>(psi, ro - 2 * g.pitch, c0, inb);
-                    pm = ld2g<T>(psi, ro - g.pitch, c0, inb);
-                    pc = ld2g<T>(psi, ro, c0, inb);
-                    pn = ld2g<T>(psi, ro + g.pitch, c0, inb);
+                    if (lo - 2 >= 0) pmm = ldpsi(ro - 2 * g.pitch);
+                    pm = ldpsi(ro - g.pitch);
+                    pc = ldpsi(ro);
+                    pn = ldpsi(ro + g.pitch);
                 }
                 apply_row(lo - 1, ld2g<T>(ua, ro - g.pitch, c0, inb), ld2g<T>(va, ro - g.pitch, c0, inb), pmm, pm, pc, fum, fvm);
                 apply_row(lo, ld2g<T>(ua, ro, c0, inb), ld2g<T>(va, ro, c0, inb), pm, pc, pn, fuc, fvc);
@@ -422,21 +447,23 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
             }
             // software pipeline: stored values of row i+1 (and psi row i+2) are loaded one iteration ahead
             D2 urn = ld2g<T>(ua, ro + g.pitch, c0, inb), vrn = ld2g<T>(va, ro + g.pitch, c0, inb);
-            if (PSI) pn = (lo + 2 < g.ny) ? ld2g<T>(psi, ro + 2 * g.pitch, c0, inb) : D2{0, 0};
+            if (PSI) pn = (lo + 2 < g.ny) ? ldpsi(ro + 2 * g.pitch) : PZ;
             D2 mn = (lo + 1 < g.ny - 1) ? mult_row(ro + g.pitch) : D2{1.0, 1.0};
             MARCH_UNROLL
             for (int i = lo; i < hi; ++i, ro += g.pitch) {
                 // issue the loads of the NEXT iteration: stored row i+2, psi row i+3, ibm row i+2
-                D2 urn2 = {0, 0}, vrn2 = {0, 0}, pn2 = {0, 0}, mn2 = {1.0, 1.0};
+                D2 urn2 = {0, 0}, vrn2 = {0, 0}, mn2 = {1.0, 1.0};
+                PsiRow pn2 = PZ;
                 if (i + 1 < hi) {
                     urn2 = ld2g<T>(ua, ro + 2 * g.pitch, c0, inb); vrn2 = ld2g<T>(va, ro + 2 * g.pitch, c0, inb);
-                    if (PSI && i + 3 < g.ny) pn2 = ld2g<T>(psi, ro + 3 * g.pitch, c0, inb);
+                    if (PSI && i + 3 < g.ny) pn2 = ldpsi(ro + 3 * g.pitch);
                     if (i + 2 < g.ny - 1) mn2 = mult_row(ro + 2 * g.pitch);
                 }
                 if (inb && i + FPF < g.ny) {
                     const long long kp = ro + FPF * g.pitch + c0;
                     pf_l2(ua + kp); pf_l2(va + kp);
                     if (PSI) pf_l2(psi + kp);
+                    if (NPSI == 2) pf_l2(psi1 + kp);
                 }
                 D2 fun, fvn;
                 apply_row(i + 1, urn, vrn, pm, pc, pn, fun, fvn);
@@ -515,17 +542,19 @@ int finalize_fast_num_partials(const Geom& g, int n_sm) {
     const dim3 gr = finalize_fast_grid(g, n_sm, &rpb);
     return (int)(gr.x * gr.y);
 }
-// psi != NULL: the pending correction u,v -= grad(psi) of the last clean-divergence iteration is applied on the fly
+// psi != NULL: the pending correction u,v -= grad(psi) of the last clean-divergence iteration is applied on the fly;
+// psi1 != NULL as well: the first iteration's correction u,v -= grad(psi1) is pending too (applied first).
 void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
-                          const void* psi, void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
-                          double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags, int n_sm,
-                          cudaStream_t s) {
+                          const void* psi, const void* psi1, void* u, void* v, const double* ibm, const uint8_t* mask,
+                          const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
+                          int n_sm, cudaStream_t s) {
     int rpb;
     const dim3 grid = finalize_fast_grid(g, n_sm, &rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define FF(T, PSI) launch_pdl(k_finalize_fast<T, PSI>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
-    if (dtype == 0) { if (psi) FF(double, true); else FF(double, false); }
-    else { if (psi) FF(float, true); else FF(float, false); }
+    const int np = psi ? (psi1 ? 2 : 1) : 0;
+#define FF(T, NP) launch_pdl(k_finalize_fast<T, NP>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (const T*)psi1, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
+    if (dtype == 0) { if (np == 2) FF(double, 2); else if (np == 1) FF(double, 1); else FF(double, 0); }
+    else { if (np == 2) FF(float, 2); else if (np == 1) FF(float, 1); else FF(float, 0); }
 #undef FF
 }
 

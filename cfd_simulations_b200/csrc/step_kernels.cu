@@ -248,9 +248,17 @@ __device__ void ctl_prepare(StepCtl* c, const CtlParams& cp) {
         const double nu_total = cp.is_f32 ? (double)(float)((float)((float)cp.nu + (float)c->in_mean_nut) + (float)cp.av)
                                           : (cp.nu + c->in_mean_nut) + cp.av;
         const double dt_visc = 0.4 * (cp.hmin * cp.hmin) / nu_total;
-        dt = fmin(dt_cfl, dt_visc);
-        dt = fmin(fmax(dt, cp.dt_min), cp.dt_max);
-        dt = (double)(float)dt;
+        if (cp.is_f32) {
+            // float32 fields: vel_max and nu_total are np.float32, so under NumPy 2 promotion the Python-float numerators
+            // are cast to float32 and both divisions, the min and the clip are float32 operations (v5.py:322-326)
+            const float fc = __fdiv_rn((float)(cp.cfl_target * cp.hmin), (float)vm);
+            const float fv = __fdiv_rn((float)(0.4 * (cp.hmin * cp.hmin)), (float)nu_total);
+            dt = (double)fminf(fmaxf(fminf(fc, fv), (float)cp.dt_min), (float)cp.dt_max);
+        } else {
+            dt = fmin(dt_cfl, dt_visc);
+            dt = fmin(fmax(dt, cp.dt_min), cp.dt_max);
+            dt = (double)(float)dt;
+        }
     }
     c->dt = dt;
     c->fs = fmin(1.0, (double)step / (double)cp.initial_steps);

@@ -181,10 +181,19 @@ def solve_pressure_gauss_seidel_fast(phi, div_u_star, dx, dy, dt, mask, iteratio
                                       _stream()), h)
     if not isinstance(phi, torch.Tensor):
         phi[...] = dp.cpu().numpy()
+    if return_info == "full":
+        return phi, it.value, last.value, _poisson_info(h)
     return (phi, it.value, last.value) if return_info else phi
 
 
-def solve_pressure_jacobi(phi, div_u_star, dx, dt, mask, sweeps, temporal_depth=0):
+def _poisson_info(h):
+    """{depth, passes, pass_bytes_per_cell} of the last b200cfd_poisson call on this handle."""
+    out = (C.c_int * 4)()
+    check(_lib.load().b200cfd_poisson_info(h, C.byref(out)), h)
+    return {"depth": out[0], "passes": out[1], "pass_bytes_per_cell": out[2]} if out[1] else {"depth": 1}
+
+
+def solve_pressure_jacobi(phi, div_u_star, dx, dt, mask, sweeps, temporal_depth=0, return_info=False):
     """The Jacobi branch of solve_pressure_fast (v5.py:336-346) on arbitrary arrays."""
     ny, nx = phi.shape
     h = _handle(ny, nx, _npdt(phi), dx, dx)
@@ -195,7 +204,9 @@ def solve_pressure_jacobi(phi, div_u_star, dx, dt, mask, sweeps, temporal_depth=
                                       int(temporal_depth), None, None, _stream()), h)
     if not isinstance(phi, torch.Tensor):
         phi[...] = dp.cpu().numpy()
-    return phi
+    if return_info == "full":
+        return phi, int(sweeps), 0.0, _poisson_info(h)
+    return (phi, int(sweeps), 0.0) if return_info else phi
 
 
 def solve_pressure_iterative(div_u_star, dx, dy, dt, mask, max_iter=500, tol=1e-7, omega=1.5, return_info=False):

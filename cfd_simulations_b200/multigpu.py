@@ -84,11 +84,20 @@ class HaloExchanger:
         self.sbuf_l, self.sbuf_r = mk(p.send_left), mk(p.send_right)
         self.rbuf_l, self.rbuf_r = mk(p.halo_left), mk(p.halo_right)
         self.bytes_per_exchange = sum(b.numel() * b.element_size() for b in (self.sbuf_l, self.sbuf_r) if b is not None)
+        # pack launches for the sides that send + unpack launches for the sides that receive, per field
+        self.launches_per_exchange = nfields * sum(b is not None for b in (self.sbuf_l, self.sbuf_r, self.rbuf_l, self.rbuf_r))
 
-    def exchange(self, fields):
+    def exchange(self, fields, marks=None):
+        """marks: optional list that receives 4 CUDA events (before pack, after pack, after send/recv, after unpack)."""
         p = self.plan
         assert len(fields) == self.nf
         ops = []
+        def mark():
+            if marks is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append(e)
+        mark()
         # post receives first, then pack and send
         if self.rbuf_l is not None:
             ops.append(dist.P2POp(dist.irecv, self.rbuf_l, p.rank - 1, self.group))
@@ -105,13 +114,16 @@ class HaloExchanger:
             ops.append(dist.P2POp(dist.isend, self.sbuf_r, p.rank + 1, self.group))
         if not ops:
             return
+        mark()
         for w in dist.batch_isend_irecv(ops):
             w.wait()
+        mark()
         for k, f in enumerate(fields):
             if self.rbuf_l is not None:
                 self.unpack(f, 0, p.halo_left, self.rbuf_l[k])
             if self.rbuf_r is not None:
                 self.unpack(f, p.own1, p.halo_right, self.rbuf_r[k])
+        mark()
 
 
 def exchange_halo_rows(buf, rank, nranks, halo_lo, halo_hi, group=None):

@@ -442,9 +442,59 @@ class OptimizedTurbulentSolver:
             check(n, self._h)
         return dict(zip(names.value.decode().split(";"), list(ms)[:n]))
 
+    def profile_slab_steps(self, n_steps):
+        """Where a slab-decomposed step's time goes (mean ms per step over n_steps, this rank, CUDA events on the compute
+        stream, stream launches instead of the graph): the kernels of step_begin one by one, the all_gather of the
+        reduction vector, the closing kernel, and pack / NCCL send-recv / unpack of the halo refresh."""
+        import torch.distributed as dist
+        if self._nranks == 1:
+            return {"kernels": self.profile_steps(n_steps)}
+        lib, h, sp = self._lib, self._h, lambda: _stream_ptr(self.device)
+        u, v = self._d["u"], self._d["v"]
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+        check(lib.b200cfd_profile_begin(h), h)
+        marks, halo_marks = [], []
+        for _ in range(n_steps):
+            e = [ev() for _ in range(5)]
+            e[0].record()
+            check(lib.b200cfd_step_begin(h, 0, sp()), h)
+            e[1].record()
+            dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+            e[2].record()
+            check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+            e[3].record()
+            hm = []
+            self._halo.exchange([u, v], marks=hm)
+            e[4].record()
+            marks.append(e); halo_marks.append(hm)
+            self._step += 1
+        names = C.create_string_buffer(1024)
+        ms = (C.c_double * 32)()
+        n = lib.b200cfd_profile_end(h, names, 1024, ms, 32)
+        if n < 0:
+            check(n, h)
+        torch.cuda.synchronize(self.device)
+        mean = lambda a, b: sum(m[a].elapsed_time(m[b]) for m in marks) / len(marks)
+        out = {"kernels": dict(zip(names.value.decode().split(";"), [round(x, 5) for x in list(ms)[:n]])),
+               "step_begin_total": round(mean(0, 1), 5), "all_gather": round(mean(1, 2), 5),
+               "step_end": round(mean(2, 3), 5), "halo_exchange_total": round(mean(3, 4), 5)}
+        if halo_marks and len(halo_marks[0]) == 4:
+            hmean = lambda a, b: sum(m[a].elapsed_time(m[b]) for m in halo_marks) / len(halo_marks)
+            out.update({"halo_pack": round(hmean(0, 1), 5), "halo_send_recv": round(hmean(1, 2), 5),
+                        "halo_unpack": round(hmean(2, 3), 5)})
+        return out
+
     # ---- introspection ----
     def launches_per_step(self):
         return int(self._lib.b200cfd_launches_per_step(self._h))
+
+    def launches_per_step_slab(self):
+        """Kernels of ours per slab step: the step's own plus the halo pack / unpack launches (NCCL's kernels not counted)."""
+        n = self.launches_per_step()
+        return n + (self._halo.launches_per_exchange if self._halo is not None else 0)
+
+    def collectives_per_step(self):
+        return "1 all_gather (128 B per rank) + 1 batched NCCL send/recv of the u, v halo columns"
 
     def clean_plan(self):
         out = (C.c_int * 8)()

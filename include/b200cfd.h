@@ -156,6 +156,9 @@ int b200cfd_fetch_scalars(b200cfd_handle* h, int64_t first_step, int n, b200cfd_
 int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uint8_t* mask,
                     double dx, double dy, double dt, int mode, int max_iter, double tol, double omega,
                     int temporal_depth, int* iters_done, double* last_change, void* stream);
+/* What the last b200cfd_poisson call did: out4 = {temporal depth used (1 = the one-sweep-per-pass kernels), HBM passes
+ * of the temporally blocked kernel (0 if it did not run), bytes per cell one such pass moves, reserved}. */
+int b200cfd_poisson_info(b200cfd_handle* h, int* out4);
 
 /* ---- one export per reference kernel, for unit parity (all device pointers, shape of the handle) ---- */
 /* compute_supg_stabilization_fast (v5.py:149-162) */

@@ -87,3 +87,23 @@ int orc_sor_v2(double* phi, const double* div, const unsigned char* mask, int ny
 }
 
 int orc_abi_version(void) { return 1; }
+
+/* OpenMP team control for the timed CPU baseline (bench.py): torchrun exports OMP_NUM_THREADS=1 to its workers, so
+ * the bench sets the team size explicitly and reports the size a parallel region REALLY gets. */
+#ifdef _OPENMP
+#include <omp.h>
+void orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int orc_get_threads(void)
+{
+    int n = 1;
+#pragma omp parallel
+    {
+#pragma omp single
+        n = omp_get_num_threads();
+    }
+    return n;
+}
+#else
+void orc_set_threads(int n) { (void)n; }
+int orc_get_threads(void) { return 1; }
+#endif

@@ -321,6 +321,15 @@ double SFX(orc_adaptive_dt)(const orc_config* c, const T* u, const T* v, const T
     double nu_total = sizeof(T) == 8 ? (c->nu + mean_nut) + c->av
                                      : (double)(float)((float)((float)c->nu + (float)mean_nut) + (float)c->av);
     double dt_visc = 0.4 * h * h / nu_total;
+    if (sizeof(T) == 4) {
+        /* float32 fields: vel_max and nu_total are np.float32, so under NumPy 2 promotion (NEP 50) the Python-float
+         * numerators are cast to float32 and both divisions, the min and the clip are float32 operations (v5.py:322-326) */
+        float fc = (float)(c->cfl_target * h) / (float)vm, fv = (float)(0.4 * (h * h)) / (float)nu_total;
+        float fd = fc < fv ? fc : fv;
+        if (fd < (float)c->dt_min) fd = (float)c->dt_min;
+        if (fd > (float)c->dt_max) fd = (float)c->dt_max;
+        return (double)fd;
+    }
     double dt = dt_cfl < dt_visc ? dt_cfl : dt_visc;
     if (dt < c->dt_min) dt = c->dt_min;
     if (dt > c->dt_max) dt = c->dt_max;

@@ -44,6 +44,12 @@ def lib():
     return _LIB
 
 
+def set_threads(n: int) -> int:
+    """Set the OpenMP team size of the oracle library and return the size a parallel region really gets."""
+    lib().orc_set_threads(int(n))
+    return int(lib().orc_get_threads())
+
+
 class OrcConfig(C.Structure):
     _fields_ = [
         ("ny", C.c_int), ("nx", C.c_int),

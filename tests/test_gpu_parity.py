@@ -370,3 +370,106 @@ def test_steps_les_branch_vs_oracle(orc, f32):
     # past step 1000 dt is neither the warm-up value nor the 1e-4 clip: the limits that read mean(nu_t) / max|u| are active
     assert all(d < 0.9e-4 for d in dts_o[-5:]) and any(2.5e-5 < d < 3.04e-5 for d in dts_o)
     sg.close()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_unclipped_adaptive_dt_vs_reference_golden(f32):
+    """cfl_target = 0.001: after step 1000 dt is the CFL value strictly between dt_min and dt_max (the unclipped branch of
+    adaptive_time_step, v5.py:322-326; float32 divisions in float32 mode), dt compared with == at every step."""
+    name = f"steps_46x150_adaptive_{'f32' if f32 else 'f64'}.npz"
+    g, _ = load(name)
+    assert 1e-6 < float(g["dts"][-1]) < 1e-4
+    _gpu_steps(name, 150, 46, f32, 15, {15}, cfl_target=0.001)
+
+
+def test_step_ladder_3000_fp64_vs_reference_golden():
+    """SURVEY section 4's step ladder: ONE float64 run of the shipped 600x180 grid from step 0 through step 3000 without
+    ever resetting `step` (the dt switch v5.py:320-326, the perturbation ramp :351 and the IBM ramp :406 are crossed the
+    natural way); u, v, phi against the reference's own fields (decimated [::4, ::4] in the fixture) after 999, 1001, 1100
+    and 3000 steps at <= 1e-12, every dt with ==, every energy_history entry."""
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    g, _ = load("steps_180x600_ladder_f64.npz")
+    k = int(g["stride"])
+    s = OptimizedTurbulentSolver(OptimizedTurbulentConfig(nx=600, ny=180, memory_efficient=False))
+    done = 0
+    for n in [int(x) for x in g["ladder"]]:
+        s.advance(n - done)
+        done = n
+        for name in ("u", "v", "phi"):
+            assert rel_l2(getattr(s, name)[::k, ::k], g[f"{name}_{n}"]) <= 1e-12, (name, n)
+    s._sync_scalars()
+    assert s.step == 3000 and [r["dt"] for r in s.scalars] == [float(x) for x in g["dts"]]
+    e = np.array([x for _, x in s.energy_history])
+    assert np.allclose(e, g["energy"], rtol=1e-12)
+    s.close()
+
+
+def _c3_inputs(N, dt):
+    """BASELINE.json configs[2] inputs at size N: disc mask of radius N/40 at (N/5, N/2),
+    rhs = 0.1 * standard_normal, dx = dy = 1/(N-1), cfg.dt = float32(5e-5)."""
+    rng = np.random.default_rng(0)
+    div = (0.1 * rng.standard_normal((N, N))).astype(dt)
+    yy, xx = np.mgrid[0:N, 0:N]
+    mask = (xx - N // 5) ** 2 + (yy - N // 2) ** 2 <= (N // 40) ** 2
+    return div, mask, 1.0 / (N - 1), float(np.float32(5e-5))
+
+
+def test_c3_poisson_replica_512_vs_oracle(K, orc):
+    """configs[2] on its own inputs at 512^2 fp64: Jacobi and red-black SOR (omega 1.5) with a fixed sweep count through
+    the one-sweep kernels (depth 1) and the TMA temporally blocked kernel (auto depth), and tolerance mode with the SAME
+    iteration count as the sequential algorithm (v5.py:212-225 as written)."""
+    N = 512
+    div, mask, h, cdt = _c3_inputs(N, np.float64)
+    z = lambda: np.zeros((N, N))
+    orc.set_threads(8)
+    pr = orc.solve_pressure_jacobi(z(), div, h, cdt, mask, 48)
+    for depth in (1, 0):
+        assert rel_l2(K.solve_pressure_jacobi(z(), div, h, cdt, mask, 48, temporal_depth=depth), pr) <= 1e-12, depth
+    for omega in (1.0, 1.5):
+        pr, _, lr = orc.solve_pressure_gauss_seidel(z(), div, h, h, cdt, mask, 40, 0.0, omega)
+        for depth in (1, 0):
+            pg, it, lg = K.solve_pressure_gauss_seidel_fast(z(), div, h, h, cdt, mask, 40, 0.0, omega=omega,
+                                                            return_info=True, temporal_depth=depth)
+            assert it == 40 and rel_l2(pg, pr) <= 1e-12, (omega, depth)
+    tol = 1e-3 * float(np.abs(div).max()) * h * h / cdt
+    for omega in (1.0, 1.5):
+        pr, itr, lr = orc.solve_pressure_gauss_seidel(z(), div, h, h, cdt, mask, 20000, tol, omega)
+        assert 1 < itr < 20000
+        for depth in (1, 0):
+            pg, itg, lg = K.solve_pressure_gauss_seidel_fast(z(), div, h, h, cdt, mask, 20000, tol, omega=omega,
+                                                             return_info=True, temporal_depth=depth)
+            assert itg == itr, (omega, depth, itg, itr)
+            assert abs(lg - lr) <= 1e-9 * abs(lr) and rel_l2(pg, pr) <= 1e-12, (omega, depth)
+
+
+def test_c2_10k_steps_drag_lift_series_vs_oracle():
+    """BASELINE.json configs[1] as written: 4096x1024 fp64, N = 10 000 steps, the drag / lift proxies and the shedding
+    probe (diagnostics.py; the reference computes none, SURVEY finding 7) every 50 steps against the oracle's series
+    (tests/golden/longrun_c2_f64_oracle.npz, minted once with tools/long_run.py --impl oracle), pointwise within 0.5 % of
+    the series' scale (north_star), the clock and the final fields (decimated [::16, ::16]) as well."""
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    fx = root / "tests" / "golden" / "longrun_c2_f64_oracle.npz"
+    if not fx.exists():
+        pytest.skip("longrun_c2_f64_oracle.npz not minted")
+    sys.path.insert(0, str(root / "tools"))
+    import long_run
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    g = np.load(fx)
+    steps, every = int(g["steps"]), int(g["every"])
+    cfg = OptimizedTurbulentConfig(nx=int(g["nx"]), ny=int(g["ny"]), memory_efficient=False)
+    s = OptimizedTurbulentSolver(cfg, setup="host")
+    out = long_run.sample_run(s, cfg, steps, every, True)
+    assert np.array_equal(out["step"], g["step"])
+    assert np.allclose(out["t"], g["t"], rtol=1e-12)
+    for k in ("cd", "cl", "vprobe"):
+        scale = np.abs(g[k]).max()
+        assert np.abs(out[k] - g[k]).max() <= 5e-3 * scale, k
+    st = int(g["final_u"].shape[0] and 16)
+    for name in ("u", "v"):
+        a, b = getattr(s, name)[::st, ::st], g["final_" + name]
+        assert rel_l2(a, b) <= 1e-9, name
+    s.close()

@@ -108,3 +108,32 @@ def test_steps_shipped_grid(f32):
 
 def test_steps_upwind_branch():
     _run_steps("steps_30x90_upwind_f64.npz", 90, 30, False, 10, {10}, use_supg=False)
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_steps_unclipped_adaptive_dt(f32):
+    """cfl_target = 0.001: after step 1000 dt is the CFL value, strictly between dt_min and dt_max (the branch of
+    adaptive_time_step, v5.py:322-326, that the clipped goldens never exercise); dt compared with == every step."""
+    name = f"steps_46x150_adaptive_{'f32' if f32 else 'f64'}.npz"
+    g, _ = load(name)
+    assert 1e-6 < float(g["dts"][-1]) < 1e-4
+    _run_steps(name, 150, 46, f32, 15, {15}, cfl_target=0.001)
+
+
+def test_step_ladder_3000_fp64():
+    """SURVEY section 4's ladder: one float64 run of the shipped 600x180 grid from step 0 through step 3000 (crossing the
+    dt switch, the perturbation ramp and the IBM ramp at step 1000 without resetting `step`), u, v, phi against the
+    reference's (decimated) fields after 999, 1001, 1100 and 3000 steps, every dt."""
+    g, _ = load("steps_180x600_ladder_f64.npz")
+    k = int(g["stride"])
+    orc.set_threads(4)
+    s = OracleTurbulentSolver(OptimizedTurbulentConfig(nx=600, ny=180, memory_efficient=False))
+    ladder = [int(x) for x in g["ladder"]]
+    for n in range(1, ladder[-1] + 1):
+        dt = s.time_step()
+        assert float(dt) == float(g["dts"][n - 1]), n
+        if n in ladder:
+            for name in ("u", "v", "phi"):
+                assert rel_l2(getattr(s, name)[::k, ::k], g[f"{name}_{n}"]) <= 1e-12, (name, n)
+    e = np.array([x for _, x in s.energy_history])
+    assert np.allclose(e, g["energy"], rtol=1e-12)

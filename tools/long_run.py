@@ -56,9 +56,13 @@ def main():
     ap.add_argument("--steps", type=int, default=150000)
     ap.add_argument("--every", type=int, default=25)
     ap.add_argument("--f64", action="store_true")
+    ap.add_argument("--nx", type=int, default=0, help="grid override (0 = the shipped 600x180); with --ny")
+    ap.add_argument("--ny", type=int, default=0)
+    ap.add_argument("--field-stride", type=int, default=0, help="also store u, v, phi[::s, ::s] of the final state")
     ap.add_argument("--out", required=True)
     a = ap.parse_args()
-    cfg = OptimizedTurbulentConfig(memory_efficient=not a.f64)          # the shipped case: 600x180, Re 600
+    kw = {"nx": a.nx, "ny": a.ny} if a.nx and a.ny else {}
+    cfg = OptimizedTurbulentConfig(memory_efficient=not a.f64, **kw)    # default: the shipped case 600x180, Re 600
     t0 = time.time()
     if a.impl == "b200":
         from cfd_simulations_b200.solver import OptimizedTurbulentSolver
@@ -71,7 +75,11 @@ def main():
     wall = time.time() - t0
     st = strouhal(out["t"], out["vprobe"], cfg, t_discard=min(10.0, 0.5 * out["t"][-1]))
     print(f"{a.impl}: {a.steps} steps, t_end {out['t'][-1]:.4f}, wall {wall:.1f} s, St {st}")
-    np.savez_compressed(a.out, impl=a.impl, steps=a.steps, every=a.every, wall_s=wall, f64=a.f64, **out)
+    if a.field_stride > 0:
+        k = a.field_stride
+        for name in ("u", "v", "phi"):
+            out["final_" + name] = np.ascontiguousarray(np.asarray(getattr(s, name))[::k, ::k])
+    np.savez_compressed(a.out, impl=a.impl, steps=a.steps, every=a.every, wall_s=wall, f64=a.f64, nx=cfg.nx, ny=cfg.ny, **out)
 
 
 if __name__ == "__main__":

@@ -43,6 +43,7 @@ struct b200cfd_handle {
     bool fast = false;                // row-marching fast kernels applicable (decided when the fields are bound)
     bool fuse_apply = false;          // clean sweep writes the corrected velocity itself: parity-green but measured SLOWER on B200 (the sweep is issue-bound), off unless B200CFD_FUSE_APPLY is set
     bool fuse_k23 = true;             // K2 + K3 in one kernel on the fast path (B200CFD_NO_FUSE_K23 turns it off)
+    bool fin_tma = false;             // finalize through the TMA-staged kernel (finalize_tma.cu); decided when the fields are bound
     bool fuse_corr = true;            // 2 clean iterations on the fast path: the second sweep applies the first correction on its load side and finalize applies both (no k_clean_apply pass); B200CFD_FUSE_CORR=0 turns it off
     // caller-owned (bound) device memory
     void *u = nullptr, *v = nullptr, *phi = nullptr, *us = nullptr, *vs = nullptr, *div = nullptr, *tau = nullptr, *nu_t = nullptr;
@@ -151,6 +152,7 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     CUC(cudaMemset(h->psi[0], 0, fb)); CUC(cudaMemset(h->psi[1], 0, fb));   // psi borders must be 0 and are never written
     h->n_part = finalize_num_partials(h->g);
     { const int nf = finalize_fast_num_partials(h->g, h->n_sm); if (nf > h->n_part) h->n_part = nf; }
+    { const int nf = finalize_tma_num_partials(h->g, h->n_sm); if (nf > h->n_part) h->n_part = nf; }
     h->n_part_used = finalize_num_partials(h->g);
     { int ntx, nty; const int nb = tile_flags_dims(h->g, &ntx, &nty); CUC(cudaMalloc(&h->flags, nb)); CUC(cudaMemset(h->flags, 3, nb)); }
     CUC(cudaMalloc(&h->ke_part, sizeof(double) * h->n_part));
@@ -197,7 +199,10 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
         CU(h, cudaSetDevice(h->device));
         launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
         CU(h, cudaDeviceSynchronize());
-        h->n_part_used = h->fast ? finalize_fast_num_partials(h->g, h->n_sm) : finalize_num_partials(h->g);
+        h->fin_tma = h->fast && h->cfg.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && h->cfg.clean_iters > 0 &&
+                     finalize_tma_ok(h->cfg.dtype, h->g, h->ua, h->va, h->psi[0], h->psi[1]);
+        h->n_part_used = h->fin_tma ? finalize_tma_num_partials(h->g, h->n_sm)
+                                    : (h->fast ? finalize_fast_num_partials(h->g, h->n_sm) : finalize_num_partials(h->g));
     }
     if (h->step_graph) { cudaGraphExecDestroy(h->step_graph); h->step_graph = nullptr; }
     if (h->begin_graph) { cudaGraphExecDestroy(h->begin_graph); h->begin_graph = nullptr; }
@@ -376,7 +381,10 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer, defer ? &fu : nullptr, defer ? &fv : nullptr,
                         defer ? &first_psi : nullptr);
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
-    if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, defer ? first_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
+    if (h->fin_tma && defer && last_psi) {
+        if (!launch_finalize_tma(dt, h->g, h->phys, h->ctl, fu, fv, last_psi, first_psi, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s))
+            h->err = "launch of the TMA finalize kernel failed";
+    } else if (h->fast) launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, defer ? first_psi : nullptr, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s);
     else launch_finalize(dt, h->g, h->phys, h->ctl, h->ua, h->va, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, s);
     ++nl;
     prof_mark(h, (defer && first_psi) ? "finalize2" : "finalize", s, pi);

@@ -172,6 +172,16 @@ __device__ __forceinline__ void predictor_point(const Geom& g, const Phys& p, co
     if (tau_out) tau_out[k] = (T)tau_o;
 }
 
+// column classes of a column (fast kernels)
+enum { COL_INTERIOR = 0, COL_INFLOW = 1, COL_OUTFLOW = 2, COL_COPY = 3 };
+__device__ __forceinline__ int col_class(const Geom& g, int c) {
+    const int cg = g.jg0 + c;
+    if (cg == 0) return COL_INFLOW;
+    if (cg == g.nxg - 1) return COL_OUTFLOW;
+    if (c == 0 || c == g.nx - 1) return COL_COPY;        // outermost halo column of a slab: no stencil
+    return COL_INTERIOR;
+}
+
 // ------------------------------------------------------------------------------------------------
 // K5 at one cell.  Reads ua, va (after clean_divergence), writes u, v (different buffers):
 //   max|div(ua,va)| (v5.py:421-422) -> BC (v5.py:424) -> IBM (:425) -> nanmax|vorticity| (:427-428)

@@ -530,8 +530,11 @@ CleanPlan clean_plan(const Geom& g, int dtype, int n_sm) {
     const int ncols = g.nx - 2, nrows = g.ny - 2;
     cp.n_strips = (ncols + cp.strip_w - 1) / cp.strip_w;
     // enough tiles for ~8 warps per SM, tile height in [32 (8 on small grids), 512]
+    // (rounded DOWN: every tile must be resident at once - one warp per tile, all tiles the same length - or the few
+    // blocks of a second wave double the kernel's time: measured r02c, 304 blocks on 296 slots)
     const int want = tune_int("B200CFD_CLEAN_WARPS_PER_SM", 8) * n_sm;
-    int nt = (want + cp.n_strips - 1) / cp.n_strips;
+    int nt = want / cp.n_strips;
+    if (nt < 1) nt = 1;
     int th = (nrows + nt - 1) / (nt > 0 ? nt : 1);
     // at least 32 rows per tile when there are enough tiles anyway; on small grids (not even 2 warps per SM) latency
     // is all that matters: go down to 8 owned rows per tile

@@ -50,8 +50,8 @@ template <> struct Sm4<float> {
 
 // MODE 0: psi_old = 0 (first iteration).  MODE 1: psi_old streamed.  MODE 2: psi_old = psi_1 streamed AND the correction
 // u,v -= grad(psi_1) applied to u, v as they are loaded (second iteration of the fused step).
-template <typename T, int MODE, int LEVELS, int NSLOT>
-__global__ void __launch_bounds__(32 * TWARPS, 2)
+template <typename T, int MODE, int LEVELS, int NSLOT, int MINB>
+__global__ void __launch_bounds__(32 * TWARPS, MINB)
 k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_v,
                   const __grid_constant__ CUtensorMap tm_p, Geom g, CleanPlan cp, T* __restrict__ pnew) {
     constexpr int NARR = MODE == 0 ? 2 : 3;
@@ -254,9 +254,18 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
 // smallest number of Kogge-Stone levels L for which what the truncated scan drops, alpha^(4 * 2^L) / (1 - alpha) relative,
 // is below 2^-(bits + 4)
 static int scan_levels(double alpha, int bits) {
-    for (int L = 2; L < 5; ++L)
+    for (int L = 3; L < 4; ++L)
         if ((double)(4 << L) * -log2(alpha) >= bits + 4 - log2(1.0 - alpha)) return L;
-    return 5;
+    return 4;
+}
+
+// ring slots per warp (3 rows each).  Measured on B200 (profiles/r02d_knobs.txt): the two-array sweep of the first
+// iteration likes the deepest ring (4 slots, 2 blocks per SM: 1.11 ms against 1.25 ms with 2 slots at 16384^2, equal at
+// 4096x1024); the three-array sweeps are better off with more resident warps than with more rows in flight (2 slots,
+// 3 blocks per SM: 1.45 / 0.046 ms against 1.76 / 0.068 ms with 4 slots at 16384^2 / 4096x1024).
+int clean_tma_default_slots(int dtype, int mode) {
+    (void)dtype;
+    return mode == 0 ? 4 : 2;
 }
 
 static int tune_env(const char* name, int dflt) {
@@ -268,33 +277,41 @@ template <typename T, int MODE, int LEVELS, int NSLOT>
 static bool launch_one(const CUtensorMap& mu, const CUtensorMap& mv, const CUtensorMap& mp, const Geom& g, const CleanPlan& cp,
                        void* pnew, int nblk, cudaStream_t s) {
     constexpr int NARR = MODE == 0 ? 2 : 3;
-    const size_t smem = (size_t)TWARPS * NSLOT * NARR * TKR * TW * sizeof(T) + TWARPS * NSLOT * sizeof(uint64_t);
+    // resident blocks per SM the ring allows (227 KB of shared memory per SM, 1 KB reserved per block); the register cap
+    // of __launch_bounds__ follows it
+    constexpr size_t SMEM = (size_t)TWARPS * NSLOT * NARR * TKR * TW * sizeof(T) + TWARPS * NSLOT * sizeof(uint64_t);
+    constexpr int FIT = (int)((227 * 1024) / (SMEM + 1024));
+    constexpr int MINB = FIT > 4 ? 4 : (FIT < 1 ? 1 : FIT);
+    auto kern = k_clean_sweep_tma<T, MODE, LEVELS, NSLOT, MINB>;
     static bool configured = false;
     if (!configured) {
-        if (cudaFuncSetAttribute(k_clean_sweep_tma<T, MODE, LEVELS, NSLOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM) != cudaSuccess) {
             cudaGetLastError();
             return false;
         }
         configured = true;
     }
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(nblk); cfg.blockDim = dim3(32 * TWARPS); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cfg.gridDim = dim3(nblk); cfg.blockDim = dim3(32 * TWARPS); cfg.dynamicSmemBytes = SMEM; cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = at; cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, k_clean_sweep_tma<T, MODE, LEVELS, NSLOT>, mu, mv, mp, g, cp, (T*)pnew) == cudaSuccess;
+    return cudaLaunchKernelEx(&cfg, kern, mu, mv, mp, g, cp, (T*)pnew) == cudaSuccess;
 }
 
 template <typename T, int MODE, int NSLOT>
 static bool launch_levels(int L, const CUtensorMap& mu, const CUtensorMap& mv, const CUtensorMap& mp, const Geom& g,
                           const CleanPlan& cp, void* pnew, int nblk, cudaStream_t s) {
-    switch (L) {
-        case 2: return launch_one<T, MODE, 2, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
-        case 3: return launch_one<T, MODE, 3, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
-        case 4: return launch_one<T, MODE, 4, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
-        default: return launch_one<T, MODE, 5, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
-    }
+    if (L <= 3) return launch_one<T, MODE, 3, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
+    return launch_one<T, MODE, 4, NSLOT>(mu, mv, mp, g, cp, pnew, nblk, s);
+}
+template <typename T, int MODE>
+static bool launch_slots(int nslot, int L, const CUtensorMap& mu, const CUtensorMap& mv, const CUtensorMap& mp, const Geom& g,
+                         const CleanPlan& cp, void* pnew, int nblk, cudaStream_t s) {
+    if (nslot <= 2) return launch_levels<T, MODE, 2>(L, mu, mv, mp, g, cp, pnew, nblk, s);
+    if (nslot == 3) return launch_levels<T, MODE, 3>(L, mu, mv, mp, g, cp, pnew, nblk, s);
+    return launch_levels<T, MODE, 4>(L, mu, mv, mp, g, cp, pnew, nblk, s);
 }
 
 // Is the TMA sweep applicable?  One-pass plan, rows of a multiple of 4 cells, 16-byte aligned bases and pitch.
@@ -320,15 +337,18 @@ bool launch_clean_sweep_tma(int dtype, const Geom& g, const CleanPlan& cp, const
     const int nblk = (ntile + TWARPS - 1) / TWARPS;
     if (nblk <= 0) return true;
     const double alpha = g.ax * g.dinv;
+    // alpha < 1/2, so 4 levels (64 columns) always suffice; 3 when alpha^32 is already below one ulp (dx >= ~0.8 dy)
     const int L = tune_env("B200CFD_CLEAN_LEVELS", scan_levels(alpha, dtype == 0 ? 53 : 30));
+    // ring slots per warp: more slots = more rows in flight per warp but fewer resident warps (shared memory)
+    const int nslot = tune_env("B200CFD_CLEAN_NSLOT", clean_tma_default_slots(dtype, mode));
     if (dtype == 0) {
-        if (mode == 0) return launch_levels<double, 0, 4>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
-        if (mode == 1) return launch_levels<double, 1, 3>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
-        return launch_levels<double, 2, 3>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
+        if (mode == 0) return launch_slots<double, 0>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
+        if (mode == 1) return launch_slots<double, 1>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
+        return launch_slots<double, 2>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
     }
-    if (mode == 0) return launch_levels<float, 0, 4>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
-    if (mode == 1) return launch_levels<float, 1, 4>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
-    return launch_levels<float, 2, 4>(L, mu, mv, mp, g, cp, psi_new, nblk, s);
+    if (mode == 0) return launch_slots<float, 0>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
+    if (mode == 1) return launch_slots<float, 1>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
+    return launch_slots<float, 2>(nslot, L, mu, mv, mp, g, cp, psi_new, nblk, s);
 }
 
 }  // namespace b200cfd

@@ -85,6 +85,12 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
                           const void* psi_or_null, const void* psi1_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,
                           const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
                           int n_sm, cudaStream_t s);
+// K5 with its rows staged by TMA (finalize_tma.cu); psi (the last pending correction) is required
+bool finalize_tma_ok(int dtype, const Geom& g, const void* ua, const void* va, const void* psi, const void* psi1);
+int finalize_tma_num_partials(const Geom& g, int n_sm);
+bool launch_finalize_tma(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va, const void* psi,
+                         const void* psi1, void* u, void* v, const double* ibm, const uint8_t* mask, const double* y,
+                         double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags, int n_sm, cudaStream_t s);
 void launch_rb1_close(StepCtl* ctl, double tol, cudaStream_t s);
 
 // ---- Poisson -----------------------------------------------------------------------------------

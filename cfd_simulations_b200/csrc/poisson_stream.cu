@@ -1,0 +1,564 @@
+// poisson_stream.cu — temporally blocked pressure-Poisson sweeps as a register-resident streaming pipeline.
+// Reference: python/flow_over_cylinder (Fischer)/v5.py:336-346 (Jacobi branch) and :202-226 (red-black Gauss-Seidel;
+// omega != 1 gives SOR, the converged-solution counterpart of v2.py:284-306).
+//
+// One warp owns a 128-column window (4 columns per lane) and streams DOWN a chunk of rows.  Rows of phi and of the
+// right-hand side arrive through a per-warp ring of TMA boxes (cp.async.bulk.tensor.2d + mbarrier, 3 rows per slot,
+// several slots ahead, zero fill outside the array).  Each row then runs through a pipeline of L "levels" held in
+// registers: level k computes row q-k of sweep k from the rows q-k-1, q-k, q-k+1 of sweep k-1 (two of them kept in
+// registers, the third just produced), x-neighbours by warp shuffle, right-hand side of row q-k re-read from the ring.
+// Jacobi: one level per sweep; red-black: two levels (red half-sweep, black half-sweep) per iteration.  The row that
+// leaves the last level is staged in shared memory and written back with a TMA store, 3 rows per box.
+// One HBM pass = L sweeps (L/2 red-black iterations) at 8 (phi in) + 8 (rhs) + 8 (phi out) B/cell; the only redundancy is
+// the 2 x H halo columns of the window (H = L rounded up to 4) and 2 x L rows per row chunk, so unlike the tile kernel
+// of poisson_tb.cu (4 shared-memory loads + 1 store per cell and sweep, 1.39 x staged area) depth costs almost nothing:
+// shared memory carries 8 B per cell and sweep (the right-hand side), everything else lives in registers.
+// Cell classes are data, not coordinates: k_stream_make_rhs folds the cylinder mask AND the non-updated border cells into
+// the right-hand side as sentinels (NaN = masked, +Inf = keep), so the kernel has no position tests at all.
+// Tolerance mode (red-black): per-iteration max|dphi| over the owned cells goes to its own slot (exact, order free); the
+// last block of a pass decides ON THE DEVICE whether the sequential algorithm would have stopped inside this pass
+// (v5.py:224-225) and, if so, with which depth the pass has to be redone from its intact input; every later launch
+// exits at once.  The host only polls the flag once per batch of passes.
+#include <cstdlib>
+#include <string>
+#include <type_traits>
+
+#include "poisson_tb.h"
+#include "tma.cuh"
+
+namespace b200cfd {
+
+#define SW 128        // window width = TMA box width
+#define SPL 4         // columns per lane
+#define SWARPS 4      // warps (independent tiles) per block
+#define SKR 3         // rows per ring slot = unroll of the row loop
+#define FULLM 0xffffffffu
+
+struct StreamCtl {            // device-resident control of a tolerance-terminated solve
+    int done;                 // tolerance reached: every later launch exits at once
+    int redo_depth;           // > 0: the stopping pass must be redone with this many iterations (from its intact input)
+    int stop_pass;            // index of the pass in which the solve stopped
+    int iters;                // iterations done when it stopped
+    double last_change;       // max|dphi| of the last iteration done
+    unsigned int blocks_done; // last-block election
+    int pad;
+};
+
+struct StreamParams {
+    int ny, nx;
+    int OW, H;                // owned columns per strip, halo columns per side
+    int tile_h;               // owned rows per row chunk (multiple of 3)
+    int n_strips, n_rchunks;
+    int own0, own1;           // slab-owned local columns (max|dphi| is taken over them only)
+    int jg0;                  // global column of local column 0 (colour parity)
+    int nact;                 // active levels of this pass (<= L); the rest pass their input through
+    int iter0;                // iterations done before this pass (bookkeeping of the stop)
+    double ax, ay, dinv, omega, scale, tol;
+};
+
+template <typename T> struct SRow;
+template <> struct SRow<double> {
+    static __device__ __forceinline__ void ld(const double* p, double (&o)[SPL]) {
+        const double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
+        o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+    }
+    static __device__ __forceinline__ void st(double* p, const double (&x)[SPL]) {
+        *reinterpret_cast<double2*>(p) = make_double2(x[0], x[1]);
+        *reinterpret_cast<double2*>(p + 2) = make_double2(x[2], x[3]);
+    }
+};
+template <> struct SRow<float> {
+    static __device__ __forceinline__ void ld(const float* p, double (&o)[SPL]) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+    }
+    static __device__ __forceinline__ void st(float* p, const double (&x)[SPL]) {
+        *reinterpret_cast<float4*>(p) = make_float4((float)x[0], (float)x[1], (float)x[2], (float)x[3]);
+    }
+};
+
+// Branch-free selects.  nvcc turns a ternary whose arms are long fp64 expressions into a (divergent, per-cell) branch;
+// here every arm is needed anyway (the classes are data), so the select is spelled in PTX.
+__device__ __forceinline__ double sel_lt(double a, double b, double x, double y) {       // a < b ? x : y   (false on NaN)
+    double o;
+    asm("{\n .reg .pred p;\n setp.lt.f64 p, %1, %2;\n selp.f64 %0, %3, %4, p;\n}" : "=d"(o) : "d"(a), "d"(b), "d"(x), "d"(y));
+    return o;
+}
+__device__ __forceinline__ double sel_nan(double r, double x, double y) {                 // isnan(r) ? x : y
+    double o;
+    asm("{\n .reg .pred p;\n setp.nan.f64 p, %1, %1;\n selp.f64 %0, %2, %3, p;\n}" : "=d"(o) : "d"(r), "d"(x), "d"(y));
+    return o;
+}
+__device__ __forceinline__ double sel_int(int c, double x, double y) {                    // c != 0 ? x : y
+    double o;
+    asm("{\n .reg .pred p;\n setp.ne.s32 p, %1, 0;\n selp.f64 %0, %2, %3, p;\n}" : "=d"(o) : "r"(c), "d"(x), "d"(y));
+    return o;
+}
+
+// rhs with the cell classes folded in: NaN = masked cell, +Inf = cell that is never updated (array / global border),
+// anything else = div.  The scale (Jacobi: dx^2/dt, v5.py:341; red-black: -1/dt, v5.py:217-219) is applied in double
+// inside the sweep, as the one-sweep kernels do, so both paths round identically in fp32 storage too.
+// tflags[tile] = 1 for every tile whose window (owned cells + halos) contains a special cell: those tiles run the version
+// of the row loop with the class selects.  (Plain stores of the same value: no atomics needed.)
+template <typename T>
+__global__ void k_stream_make_rhs(int ny, int nx, long long pitch, int jg0, int nxg, const T* __restrict__ div,
+                                  const uint8_t* __restrict__ mask, T* __restrict__ out, uint8_t* __restrict__ tflags,
+                                  int OW, int H, int tile_h, int VH, int n_strips, int n_rchunks) {
+    const T nan_t = (T)__longlong_as_double(0x7ff8000000000000ll), inf_t = (T)__longlong_as_double(0x7ff0000000000000ll);
+    const long long n = (long long)ny * pitch;
+    for (long long k = blockIdx.x * 256ll + threadIdx.x; k < n; k += (long long)gridDim.x * 256ll) {
+        const int i = (int)(k / pitch), j = (int)(k - (long long)i * pitch), jg = jg0 + j;
+        const bool upd = i >= 1 && i < ny - 1 && j >= 1 && j < nx - 1 && jg >= 1 && jg < nxg - 1;
+        const bool msk = mask && mask[k];
+        out[k] = !upd ? inf_t : (msk ? nan_t : div[k]);
+        if ((!upd || msk) && j < nx) {
+            const int s0 = max((j - H) / OW, 0), s1 = min((j + H) / OW, n_strips - 1);
+            const int c0 = max((i - VH) / tile_h, 0), c1 = min((i + VH) / tile_h, n_rchunks - 1);
+            for (int c = c0; c <= c1; ++c)
+                for (int s = s0; s <= s1; ++s) tflags[c * n_strips + s] = 1;
+        }
+    }
+}
+
+// MODE 0: Jacobi, L sweeps per pass.  MODE 1: red-black Gauss-Seidel / SOR, L/2 iterations per pass (L even).
+// role 0: normal pass (exits at once when ctl->done); role 1: redo of pass `pass_index` with ctl->redo_depth iterations.
+// SOR: omega != 1 (the relaxation step is compiled in only then: omega = 1 must stay the exact Gauss-Seidel update).
+// CHECK: accumulate the per-iteration max|dphi| (tolerance mode).
+template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
+__global__ void __launch_bounds__(32 * SWARPS, 2)
+k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_rhs,
+                 const __grid_constant__ CUtensorMap tm_out, StreamParams P, unsigned long long* __restrict__ slots,
+                 StreamCtl* __restrict__ ctl, int role, int pass_index, const uint8_t* __restrict__ tflags) {
+    constexpr int ARR = SKR * SW;                 // elements per slot (3 rows)
+    constexpr int KEEP = (L + SKR - 1) / SKR;     // rhs slots behind the current one whose rows are still needed
+    constexpr int NSR = NS + KEEP;                // rhs ring: NS slots of lead + the ones the pipeline still reads
+    constexpr int WARP_ELEMS = (NS + NSR + 2) * ARR;   // phi ring, rhs ring, 2 staging buffers of 3 output rows
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    int nact = P.nact;
+    if (ctl) {
+        const int done = *reinterpret_cast<volatile int*>(&ctl->done);
+        if (role == 0) { if (done) return; }
+        else {
+            const int rd = *reinterpret_cast<volatile int*>(&ctl->redo_depth), sp = *reinterpret_cast<volatile int*>(&ctl->stop_pass);
+            if (!done || rd <= 0 || sp != pass_index) return;
+            nact = MODE == 1 ? 2 * rd : rd;
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tile = blockIdx.x * SWARPS + warp;
+    const bool active = tile < P.n_strips * P.n_rchunks;
+    T* ring_p = reinterpret_cast<T*>(smem_raw) + (size_t)warp * WARP_ELEMS;      // phi ring: NS slots
+    T* ring_r = ring_p + NS * ARR;                                               // rhs ring: NSR slots
+    T* stage = ring_r + NSR * ARR;                                               // 2 x 3 output rows (dense, OW per row)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)SWARPS * WARP_ELEMS * sizeof(T)) + warp * NS;
+    double ch[MODE == 1 ? L / 2 : 1];
+#pragma unroll
+    for (int t = 0; t < (MODE == 1 ? L / 2 : 1); ++t) ch[t] = 0.0;
+    if (active) {
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < NS; ++k) mbar_init(&bars[k], 1);
+            mbar_fence_init();
+        }
+        __syncwarp();
+        const int s = tile % P.n_strips, rc = tile / P.n_strips;
+        const int x0 = s * P.OW;                                  // first owned column
+        const int jw0 = x0 - P.H;                                 // window origin (multiple of 4; may be negative)
+        const int c0 = jw0 + SPL * lane;
+        const int r0 = rc * P.tile_h, r1 = min(r0 + P.tile_h, P.ny);
+        // ingest rows q0 .. ; the row leaving level L at ingest step q is q - L.  q0 is chosen so that (i) level L's first
+        // valid row (q0 + L) is <= r0 and (ii) row r0 leaves the pipeline (at ingest step r0 + L) as the FIRST row of a chunk
+        // (stores are whole 3-row boxes): q0 = r0 - L - e with (2L + e) % 3 == 0
+        constexpr int E = (3 - (2 * L) % 3) % 3;
+        const int q0 = r0 - L - E;
+        const int NCH = (r1 + L - q0 + SKR - 1) / SKR;            // chunks until row r1 - 1 has left the pipeline
+        // chunk k: phi rows into slot k % NS of the phi ring, rhs rows into slot k % NSR of the rhs ring (one mbarrier per
+        // phi slot covers both boxes)
+        auto issue = [&](int k) {
+            const int slot = k % NS;
+            mbar_expect_tx(&bars[slot], (uint32_t)(2 * ARR * sizeof(T)));
+            tma_load_2d(ring_p + slot * ARR, &tm_in, jw0, q0 + SKR * k, &bars[slot]);
+            tma_load_2d(ring_r + (k % NSR) * ARR, &tm_rhs, jw0, q0 + SKR * k, &bars[slot]);
+        };
+        if (lane == 0) {
+            const int n0 = NCH < NS ? NCH : NS;
+            for (int k = 0; k < n0; ++k) issue(k);
+        }
+        // column flags as multiplicative masks: owned by this tile AND by this slab (max|dphi| only)
+        double ownm[SPL];
+#pragma unroll
+        for (int m = 0; m < SPL; ++m) {
+            const int c = c0 + m;
+            ownm[m] = (c >= x0 && c < x0 + P.OW && c >= P.own0 && c < P.own1 && c < P.nx) ? 1.0 : 0.0;
+        }
+        // colour of this lane's columns: c0 is a multiple of 4, so cells 0, 2 have the parity of (row + jg0), cells 1, 3 the other
+        const int colpar = P.jg0 & 1;
+        const double ax = P.ax, ay = P.ay, dinv = P.dinv, omega = P.omega, nscale = -P.scale;
+        const double INF = __longlong_as_double(0x7ff0000000000000ll);
+
+        // pipeline registers: R[k] = the two newest rows that entered level k+1 (k = 0: phi as loaded)
+        double R[L][3][SPL];
+#pragma unroll
+        for (int k = 0; k < L; ++k)
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+#pragma unroll
+                for (int m = 0; m < SPL; ++m) R[k][j][m] = 0.0;
+
+        const int scol = SPL * lane - P.H;                          // this lane's first column inside the staged (owned) row
+        const bool st_lane = scol >= 0 && scol + SPL <= P.OW;
+        const T* ring_rl = ring_r + SPL * lane;
+        // folded coefficients (the same in both code paths below, so a cell's value does not depend on which tile - plain or
+        // special - computed it: redundant halo copies stay bit-identical to the owner's value)
+        const double q4 = 0.25 * nscale, axd = ax * dinv, ayd = ay * dinv, nsd = nscale * dinv;
+
+        // The row loop, in two versions chosen per tile (warp-uniform): SPECIAL tiles contain masked cells, never-updated
+        // border cells or inactive levels and carry the class selects; plain tiles (almost all of them) are pure arithmetic.
+        auto run = [&](auto special_tag) {
+            constexpr bool SPECIAL = decltype(special_tag)::value;
+            // red-black: which cells of a row have the colour of a level is a compile-time fact once the parity PB of
+            // (first row of the chunk + colour offset of the window) is fixed; the chunk body exists in both parities and a
+            // warp-uniform branch picks one per chunk (a branch per LEVEL gets if-converted: both arms issue, predicated)
+            // one level: row `row` of sweep k+1 from rows S (row-1), C (row), N (row+1) of sweep k and the rhs of `row`.
+            // Straight-line code: shuffles are unconditional, the parts that do not depend on the x-neighbours come first.
+            auto level = [&](auto pb_tag, int k, int jrow, int row, const double (&S)[SPL], const double (&C)[SPL],
+                             const double (&N)[SPL], const T* rhs_row, double (&out)[SPL]) {
+                constexpr int PB = decltype(pb_tag)::value;
+                double r[SPL];
+                SRow<T>::ld(rhs_row, r);
+                const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
+                const int act = k < nact;                               // warp-uniform (always true in plain tiles)
+                if (MODE == 0) {
+#pragma unroll
+                    for (int m = 0; m < SPL; ++m) {
+                        const double ns = N[m] + S[m], rq = r[m] * q4;
+                        const double e = m < SPL - 1 ? C[(m + 1) % SPL] : En, w = m > 0 ? C[(m + SPL - 1) % SPL] : Wn;
+                        const double v = Rnd<T>::r(fma(0.25, (e + w) + ns, rq));
+                        if (SPECIAL) {
+                            // updated cell -> v, masked (NaN) -> 0 (v5.py:345), never-updated border (+Inf) -> kept
+                            const double o = sel_lt(fabs(r[m]), INF, v, sel_nan(r[m], 0.0, C[m]));
+                            out[m] = sel_int(act, o, C[m]);
+                        } else out[m] = v;
+                    }
+                } else {
+                    // colour of level k: even k = first colour ((i + j) odd, v5.py:215), odd k = second.  c0 is a multiple
+                    // of 4, so cells 0, 2 have the parity of (row + jg0) and cells 1, 3 the other one (warp-uniform branch).
+                    // row = q + jrow with (q + colpar) & 1 == PB, jrow = j - 1 - k a compile-time offset
+                    const int want = (k & 1) ? 0 : 1;
+                    const bool even_cells = (((PB + jrow) % 2 + 2) % 2) == want;       // compile time
+                    const int rown = row >= r0 && row < r1;
+                    auto cell = [&](int m, double e, double w) {
+                        const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
+                        double pn = fma(axd, e + w, t);
+                        if (SOR) pn = fma(omega, pn - C[m], C[m]);
+                        pn = Rnd<T>::r(pn);
+                        if (SPECIAL) pn = sel_int(act, sel_lt(fabs(r[m]), INF, pn, C[m]), C[m]);   // masked / border / inactive: kept
+                        out[m] = pn;
+                        if (CHECK) ch[k / 2] = fmax(ch[k / 2], sel_int(rown, fabs(pn - C[m]) * ownm[m], 0.0));
+                    };
+                    if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
+                    else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }
+                }
+            };
+            int nstore = 0;
+            for (int k = 0; k < NCH; ++k) {
+                const int slot = k % NS;
+                mbar_wait(&bars[slot], (uint32_t)((k / NS) & 1));
+                const T* sp = ring_p + slot * ARR + SPL * lane;
+                const int q = q0 + SKR * k;
+                T* sg = stage + (nstore & 1) * ARR;
+                // rhs rows of the chunks k, k-1, ... (this lane's columns): the level that computes row q + j - 1 - lv reads
+                // row (j - 1 - lv) mod 3 of chunk k + floor((j - 1 - lv) / 3), all compile-time offsets
+                const T* rb[KEEP + 2];
+                {
+                    const int km = k % NSR;
+#pragma unroll
+                    for (int o = 0; o < KEEP + 2; ++o) { int sl = km - o; if (sl < 0) sl += NSR; rb[o] = ring_rl + sl * ARR; }
+                }
+                const int orow = q - L;                                  // first row leaving the pipeline in this chunk
+                const bool do_store = orow >= r0 && orow < r1;          // whole chunks by construction
+                if (do_store && nstore >= 2) {                           // the staging buffer's previous TMA store has read it
+                    if (lane == 0) tma_store_wait_read<1>();
+                    __syncwarp();
+                }
+                auto body = [&](auto pb_tag) {
+#pragma unroll
+                    for (int j = 0; j < SKR; ++j) {
+                        // ring row j of this slot = phi row q + j enters level 1 as its north row
+                        SRow<T>::ld(sp + j * SW, R[0][(j + 2) % 3]);
+#pragma unroll
+                        for (int lv = 0; lv < L; ++lv) {
+                            const int row = q + j - 1 - lv;                  // row computed by level lv + 1
+                            const int off = j - 1 - lv;                      // compile time after unrolling
+                            const int back = off >= 0 ? 0 : (-off + SKR - 1) / SKR, jr = off + back * SKR;
+                            double out[SPL];
+                            level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
+                            if (lv + 1 < L) {
+#pragma unroll
+                                for (int m = 0; m < SPL; ++m) R[lv + 1][(j + 2) % 3][m] = out[m];
+                            } else if (do_store && st_lane) {
+                                SRow<T>::st(sg + j * P.OW + scol, out);
+                            }
+                        }
+                    }
+                };
+                if (MODE == 1 && ((q + colpar) & 1)) body(std::integral_constant<int, 1>{});
+                else body(std::integral_constant<int, 0>{});
+                if (do_store) {
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        tma_store_2d(&tm_out, x0, orow, sg);             // 3 dense rows of the OW owned columns
+                        tma_store_commit();
+                    }
+                    ++nstore;
+                }
+                __syncwarp();
+                // the phi slot of chunk k is free now; the rhs of chunk k + NS overwrites that of chunk k - KEEP, which no
+                // level reads any more (level L of the next chunk reaches back to chunk k + 1 - KEEP)
+                if (lane == 0 && k + NS < NCH) issue(k + NS);
+            }
+        };
+        const bool special = nact < L || (tflags != nullptr && tflags[tile] != 0);
+        if (special) run(std::true_type{}); else run(std::false_type{});
+        if (lane == 0) tma_store_wait<0>();
+    }
+    // ---- per-iteration max|dphi| over the owned cells -> slots; the last block closes the pass
+    if (MODE == 1 && CHECK) {
+        __shared__ double s_red[SWARPS][L / 2];
+#pragma unroll
+        for (int t = 0; t < L / 2; ++t) {
+            const double w = warp_max(ch[t]);
+            if (lane == 0) s_red[warp][t] = w;
+        }
+        __syncthreads();
+        if (threadIdx.x < L / 2) {
+            double w = 0.0;
+            for (int k = 0; k < SWARPS; ++k) w = fmax(w, s_red[k][threadIdx.x]);
+            if (w > 0.0) atomicMax(&slots[threadIdx.x], (unsigned long long)__double_as_longlong(w));
+        }
+        if (ctl && role == 0) {
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const unsigned int prev = atomicAdd(&ctl->blocks_done, 1u);
+                if (prev == gridDim.x - 1) {
+                    __threadfence();
+                    const int niter = nact / 2;
+                    int stop = 0;
+                    double last = 0.0;
+                    for (int t = 0; t < niter; ++t) {
+                        last = __longlong_as_double((long long)atomicAdd(&slots[t], 0ull));
+                        if (last < P.tol) { stop = t + 1; break; }
+                    }
+                    ctl->last_change = last;
+                    if (stop) {
+                        ctl->iters = P.iter0 + stop;
+                        ctl->stop_pass = pass_index;
+                        ctl->redo_depth = stop < niter ? stop : 0;
+                        __threadfence();
+                        ctl->done = 1;
+                    } else {
+                        ctl->iters = P.iter0 + niter;
+                    }
+                    for (int t = 0; t < L / 2; ++t) slots[t] = 0ull;
+                    ctl->blocks_done = 0u;
+                }
+            }
+        }
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------------------------------
+struct PoissonStream {
+    void* rhs_s = nullptr;
+    void* alt = nullptr;
+    size_t bytes = 0;
+    unsigned long long* slots = nullptr;   // 8 entries
+    StreamCtl* ctl = nullptr;
+    uint8_t* tflags = nullptr;             // one byte per tile: its window contains masked / never-updated cells
+    size_t tflags_cap = 0;
+    int last_depth = 0, last_passes = 0;
+};
+static std::string g_stream_err;
+const char* poisson_stream_error() { return g_stream_err.c_str(); }
+void poisson_stream_destroy(PoissonStream* ps) {
+    if (!ps) return;
+    cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->tflags);
+    delete ps;
+}
+void poisson_stream_info(const PoissonStream* ps, int* depth, int* passes) {
+    *depth = ps ? ps->last_depth : 0;
+    *passes = ps ? ps->last_passes : 0;
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return (e && *e) ? atoi(e) : dflt;
+}
+
+template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
+static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
+                         unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
+    constexpr int KEEP = (L + SKR - 1) / SKR;
+    const size_t smem = (size_t)SWARPS * (NS + NS + KEEP + 2) * SKR * SW * sizeof(T) + SWARPS * NS * sizeof(uint64_t);
+    auto kern = k_poisson_stream<T, MODE, L, NS, SOR, CHECK>;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            cudaGetLastError(); g_stream_err = "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"; return -1;
+        }
+        configured = true;
+    }
+    const int ntile = P.n_strips * P.n_rchunks;
+    kern<<<(ntile + SWARPS - 1) / SWARPS, 32 * SWARPS, smem, s>>>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags);
+    if (cudaPeekAtLastError() != cudaSuccess) { g_stream_err = cudaGetErrorString(cudaGetLastError()); return -1; }
+    return 0;
+}
+
+// pipeline depths instantiated: 2 and 6 levels (a shallower pass runs in the deeper pipeline with inactive levels)
+#define STREAM_NS 2
+template <typename T, int MODE, bool SOR, bool CHECK>
+static int stream_depth(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
+                        unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
+    if (L <= 2) return stream_launch<T, MODE, 2, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    return stream_launch<T, MODE, 6, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+}
+template <typename T, int MODE>
+static int stream_dispatch(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
+                           unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
+    if (MODE == 0) return stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    const bool sor = P.omega != 1.0, chk = slots != nullptr;
+    if (sor) return chk ? stream_depth<T, MODE, true, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
+                        : stream_depth<T, MODE, true, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    return chk ? stream_depth<T, MODE, false, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
+               : stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+}
+
+bool poisson_stream_enabled() {
+    static const int on = env_int("B200CFD_POISSON_STREAM", 1);
+    return on != 0 && tma_encoder() != nullptr;
+}
+
+// Runs `iters` sweeps (mode 0) / iterations (mode 1) on (phi, div, mask).  depth: iterations or sweeps per pass (0 = auto).
+// tol > 0 (mode 1): stop at the first iteration with max|dphi| < tol, exactly as the sequential algorithm; the host polls
+// the device flag once per `poll` passes.  Returns 0 and *iters_done = 0 when the shape is not supported.
+int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, int n_sm, void* phi, const void* div,
+                       const uint8_t* mask, double scale, double omega, int iters, int depth, int* iters_done,
+                       cudaStream_t s, double tol, double* last_change) {
+    *iters_done = 0;
+    const int es = dtype == 0 ? 8 : 4;
+    if (iters <= 0) return 0;
+    if (((uintptr_t)phi % 16) || ((g.pitch * es) % 16) || g.nx < 64 || g.ny < 16 || g.nx % 4) return 0;
+    if (!*pps) {
+        PoissonStream* ps = new PoissonStream();
+        if (cudaMalloc(&ps->slots, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&ps->ctl, sizeof(StreamCtl)) != cudaSuccess) {
+            cudaGetLastError(); g_stream_err = "cudaMalloc(control)"; delete ps; return -1;
+        }
+        *pps = ps;
+    }
+    PoissonStream* ps = *pps;
+    const size_t bytes = (size_t)g.ny * g.pitch * es;
+    if (ps->bytes < bytes) {
+        cudaFree(ps->rhs_s); cudaFree(ps->alt); ps->rhs_s = ps->alt = nullptr; ps->bytes = 0;
+        if (cudaMalloc(&ps->rhs_s, bytes) != cudaSuccess || cudaMalloc(&ps->alt, bytes) != cudaSuccess) {
+            cudaGetLastError(); g_stream_err = "cudaMalloc of the temporal-blocking scratch failed"; return -1;
+        }
+        ps->bytes = bytes;
+    }
+    // levels per pass
+    int per = depth > 0 ? depth : (mode == 0 ? 6 : 3);             // sweeps / iterations per pass
+    if (mode == 0) { if (per > 6) per = 6; }
+    else if (per > 3) per = 3;
+    if (per > iters) per = iters;
+    int L = mode == 0 ? per : 2 * per;
+    L = L <= 2 ? 2 : 6;                                             // instantiated pipeline depths
+    const int cap = mode == 0 ? L : L / 2;                          // sweeps / iterations one pass of this depth can hold
+    StreamParams P;
+    P.ny = g.ny; P.nx = g.nx; P.own0 = g.own0; P.own1 = g.own1; P.jg0 = g.jg0;
+    P.ax = g.ax; P.ay = g.ay; P.dinv = g.dinv; P.omega = omega; P.scale = scale; P.tol = tol;
+    P.H = (L + 3) / 4 * 4;
+    P.OW = SW - 2 * P.H;
+    P.n_strips = (g.nx + P.OW - 1) / P.OW;
+    // row chunks: every tile resident at once (one warp per tile); ~6 warps per SM
+    const int want = env_int("B200CFD_STREAM_WARPS_PER_SM", 8) * n_sm;
+    int nrc = want / P.n_strips;
+    if (nrc < 1) nrc = 1;
+    int th = (g.ny + nrc - 1) / nrc;
+    th = (th + SKR - 1) / SKR * SKR;
+    if (th < 4 * SKR) th = 4 * SKR;
+    P.tile_h = th;
+    P.n_rchunks = (g.ny + th - 1) / th;
+    const long long n = (long long)g.ny * g.pitch;
+    const int nb = (int)((n + 255) / 256 < 148 * 32 ? (n + 255) / 256 : 148 * 32);
+    const size_t ntile = (size_t)P.n_strips * P.n_rchunks;
+    if (ps->tflags_cap < ntile) {
+        cudaFree(ps->tflags); ps->tflags = nullptr; ps->tflags_cap = 0;
+        if (cudaMalloc(&ps->tflags, ntile) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(tile flags)"; return -1; }
+        ps->tflags_cap = ntile;
+    }
+    if (cudaMemsetAsync(ps->tflags, 0, ntile, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile flags)"; return -1; }
+    const int VH = L + 3;                                           // rows above / below a chunk its pipeline touches
+    if (dtype == 0) k_stream_make_rhs<double><<<nb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
+                                                                  ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
+    else k_stream_make_rhs<float><<<nb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const float*)div, mask, (float*)ps->rhs_s,
+                                                    ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
+    CUtensorMap m_phi, m_alt, m_rhs, o_phi, o_alt;
+    if (!tma_make_2d(&m_phi, dtype, phi, g.nx, g.ny, g.pitch, SW, SKR) || !tma_make_2d(&m_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, SW, SKR) ||
+        !tma_make_2d(&m_rhs, dtype, ps->rhs_s, g.nx, g.ny, g.pitch, SW, SKR) ||
+        !tma_make_2d(&o_phi, dtype, phi, g.nx, g.ny, g.pitch, P.OW, SKR) || !tma_make_2d(&o_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, P.OW, SKR)) {
+        g_stream_err = "cuTensorMapEncodeTiled failed"; return -1;
+    }
+    const bool check = tol > 0.0 && mode == 1;
+    if (check) {
+        if (cudaMemsetAsync(ps->ctl, 0, sizeof(StreamCtl), s) != cudaSuccess || cudaMemsetAsync(ps->slots, 0, 8 * sizeof(unsigned long long), s) != cudaSuccess) {
+            g_stream_err = "cudaMemsetAsync(control)"; return -1;
+        }
+    }
+    void* cur = phi; void* nxt = ps->alt;
+    int done = 0, pass = 0;
+    ps->last_depth = cap; ps->last_passes = 0;
+    const int poll = env_int("B200CFD_STREAM_POLL", 32);
+    auto launch = [&](int role, int d) -> int {
+        P.nact = mode == 0 ? d : 2 * d;
+        P.iter0 = done;
+        const CUtensorMap& mi = cur == phi ? m_phi : m_alt;
+        const CUtensorMap& mo = cur == phi ? o_alt : o_phi;
+        unsigned long long* sl = check ? ps->slots : nullptr;
+        StreamCtl* ct = check ? ps->ctl : nullptr;
+        if (dtype == 0) return mode == 0 ? stream_dispatch<double, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s)
+                                         : stream_dispatch<double, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s);
+        return mode == 0 ? stream_dispatch<float, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s)
+                         : stream_dispatch<float, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s);
+    };
+    StreamCtl hc;
+    bool stopped = false;
+    while (done < iters) {
+        const int d = iters - done < cap ? iters - done : cap;     // the last pass may be shallower
+        if (launch(0, d)) return -1;
+        if (check && launch(1, d)) return -1;                       // redo of this pass if the stop fell inside it (else exits at once)
+        ++ps->last_passes;
+        void* t = cur; cur = nxt; nxt = t;
+        done += d; ++pass;
+        if (check && (pass % poll == 0 || done >= iters)) {
+            if (cudaMemcpyAsync(&hc, ps->ctl, sizeof hc, cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) {
+                g_stream_err = "reading the convergence flag failed"; return -1;
+            }
+            if (hc.done) { stopped = true; break; }
+        }
+    }
+    if (check) {
+        if (stopped) {
+            // the result is what pass hc.stop_pass wrote: pass p reads (p even ? phi : alt) and writes the other one
+            done = hc.iters;
+            cur = (hc.stop_pass & 1) ? phi : ps->alt;
+            ps->last_passes = hc.stop_pass + 1;
+        }
+        if (last_change) *last_change = hc.last_change;
+    }
+    if (cur != phi && cudaMemcpyAsync(phi, cur, bytes, cudaMemcpyDeviceToDevice, s) != cudaSuccess) { g_stream_err = "copy back"; return -1; }
+    *iters_done = done;
+    return 0;
+}
+
+}  // namespace b200cfd

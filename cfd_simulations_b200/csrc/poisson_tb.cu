@@ -15,9 +15,11 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
+#include <cstdlib>
 #include <string>
 
 #include "poisson_tb.h"
+#include "tma.cuh"
 
 namespace b200cfd {
 
@@ -35,9 +37,12 @@ struct PoissonTB {
     size_t bytes = 0;
     unsigned long long* slots = nullptr;   // per-iteration max|dphi| of the last pass (TB_MAX_DEPTH entries)
     int last_depth = 0, last_passes = 0;   // what the last solve did (b200cfd_poisson_info)
+    PoissonStream* stream = nullptr;       // state of the streaming-pipeline kernel (poisson_stream.cu)
+    bool last_stream = false;
 };
 
 void poisson_tb_info(const PoissonTB* tb, int* depth, int* passes) {
+    if (tb && tb->last_stream) { poisson_stream_info(tb->stream, depth, passes); return; }
     *depth = tb ? tb->last_depth : 0;
     *passes = tb ? tb->last_passes : 0;
 }
@@ -45,29 +50,8 @@ void poisson_tb_info(const PoissonTB* tb, int* depth, int* passes) {
 void poisson_tb_destroy(PoissonTB* tb) {
     if (!tb) return;
     cudaFree(tb->rhs_s); cudaFree(tb->alt); cudaFree(tb->slots);
+    poisson_stream_destroy(tb->stream);
     delete tb;
-}
-
-// ---- PTX wrappers: mbarrier + TMA ----------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
-    asm volatile(
-        "{\n .reg .pred p;\n"
-        "WAIT_%=:\n"
-        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        " @p bra DONE_%=;\n"
-        " bra WAIT_%=;\n"
-        "DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                 ::"r"(smem_u32(dst)), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
 }
 
 struct TBParams {
@@ -186,15 +170,15 @@ k_poisson_tb(const __grid_constant__ CUtensorMap tm_phi, const __grid_constant__
 
 // ---- host side -----------------------------------------------------------------------------------
 static int tb_init(PoissonTB** ptb, size_t bytes) {
-    if (!*ptb) {
-        PoissonTB* tb = new PoissonTB();
+    if (!*ptb || !(*ptb)->encode) {
+        PoissonTB* tb = *ptb ? *ptb : new PoissonTB();
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult q;
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) {
-            cudaGetLastError(); g_tb_err = "cuTensorMapEncodeTiled is not available from this driver"; delete tb; return -1;
+            cudaGetLastError(); g_tb_err = "cuTensorMapEncodeTiled is not available from this driver"; if (!*ptb) delete tb; return -1;
         }
         tb->encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
-        if (cudaMalloc(&tb->slots, TB_MAX_DEPTH * sizeof(unsigned long long)) != cudaSuccess) { g_tb_err = "cudaMalloc(slots)"; delete tb; return -1; }
+        if (cudaMalloc(&tb->slots, TB_MAX_DEPTH * sizeof(unsigned long long)) != cudaSuccess) { g_tb_err = "cudaMalloc(slots)"; if (!*ptb) delete tb; return -1; }
         *ptb = tb;
     }
     PoissonTB* tb = *ptb;
@@ -266,6 +250,15 @@ static int tb_run(PoissonTB** ptb, int dtype, int mode, const Geom& g, void* phi
     *iters_done = 0;
     const int es = dtype == 0 ? 8 : 4;
     if (iters <= 0) return 0;
+    if (poisson_stream_enabled()) {
+        // default: the register-resident streaming pipeline; falls through to the tile kernel below when not applicable
+        if (!*ptb) *ptb = new PoissonTB();
+        (*ptb)->last_stream = false;
+        const int rc = poisson_stream_run(&(*ptb)->stream, dtype, mode, g, 148, phi, div, mask, scale, omega, iters, depth, iters_done, s,
+                                          tol, last_change);
+        if (rc < 0) { g_tb_err = poisson_stream_error(); return -1; }
+        if (*iters_done > 0) { (*ptb)->last_stream = true; return 0; }
+    }
     if (depth <= 0) depth = mode == 0 ? 4 : 3;
     if (depth > TB_MAX_DEPTH) depth = TB_MAX_DEPTH;
     if (depth > iters) depth = iters;

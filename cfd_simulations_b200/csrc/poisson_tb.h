@@ -15,4 +15,16 @@ int poisson_tb_jacobi(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* 
 int poisson_tb_rbsor(PoissonTB** tb, int dtype, const Geom& g, int n_sm, void* phi, const void* div, const uint8_t* mask,
                      double inv_dt, double omega, int iters, int depth, int* iters_done, cudaStream_t s, double tol = 0.0,
                      double* last_change = nullptr);   // tol > 0: stops at the first iteration with max|dphi| < tol (synchronises per pass)
+
+// ---- poisson_stream.cu: the register-resident streaming pipeline (default); same contract as the entries above ----
+struct PoissonStream;
+bool poisson_stream_enabled();                       // B200CFD_POISSON_STREAM=0 selects the shared-memory tile kernel above
+const char* poisson_stream_error();
+void poisson_stream_destroy(PoissonStream* ps);
+void poisson_stream_info(const PoissonStream* ps, int* depth, int* passes);
+// mode 0: Jacobi (scale = dx^2/dt), mode 1: red-black (scale = -1/dt).  tol > 0 (mode 1): device-side stop at exactly the
+// iteration the sequential algorithm stops at; the host polls once per batch of passes.
+int poisson_stream_run(PoissonStream** ps, int dtype, int mode, const Geom& g, int n_sm, void* phi, const void* div,
+                       const uint8_t* mask, double scale, double omega, int iters, int depth, int* iters_done,
+                       cudaStream_t s, double tol, double* last_change);
 }  // namespace b200cfd

@@ -112,15 +112,6 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
     rv = axpy_pred<T>(vc, dt, cv, lv);
 }
 
-// column classes of one lane's two columns
-enum { COL_INTERIOR = 0, COL_INFLOW = 1, COL_OUTFLOW = 2, COL_COPY = 3 };
-__device__ __forceinline__ int col_class(const Geom& g, int c) {
-    const int cg = g.jg0 + c;
-    if (cg == 0) return COL_INFLOW;
-    if (cg == g.nxg - 1) return COL_OUTFLOW;
-    if (c == 0 || c == g.nx - 1) return COL_COPY;        // outermost halo column of a slab: no stencil
-    return COL_INTERIOR;
-}
 
 template <typename T, bool TAU>
 __global__ void __launch_bounds__(FBT, 5)

@@ -78,6 +78,10 @@ def reference_arm(args):
                       "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+FP64_FLOP_PER_CELL = 300       # from the ncu instruction mix of k_euler_step (see the roofline note)
+FP64_PEAK_TFLOPS = 36.8        # measured: profiles/r02a_ubench_chain.txt
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -153,7 +157,14 @@ def main():
         roof = {"bound": "hbm", "kernel": "k_euler_step (fused HLLC fluxes + update + BC + wedge + dt reduction) + k_euler_ctl_end",
                 "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                 "algo_bytes_per_cell": ALGO_BYTES, "ms_per_launch": kms,
-                "note": "arithmetic is float64 as in the reference: the binding unit is the FP64 pipe, not HBM (DESIGN.md)"}
+                "note": "arithmetic is float64 as in the reference: the kernel is bound by instruction issue, not HBM (DESIGN.md 9)",
+                # second roof: fp64.  ~210 fp64 math instructions per cell (ncu, profiles/r01d_euler_full.md: ~1000 thread
+                # instructions per cell, 21 % of them DFMA/DADD/DMUL; 45 % of those are FMAs) ~ 300 flop per cell; the peak is
+                # the dependent-free DFMA rate measured on this pool's B200 with tools/ubench_chain.cu
+                "fp64": {"flop_per_cell": FP64_FLOP_PER_CELL, "achieved": FP64_FLOP_PER_CELL * cells / (kms * 1e-3) / 1e12,
+                         "peak": FP64_PEAK_TFLOPS, "unit": "TFLOP/s",
+                         "frac": FP64_FLOP_PER_CELL * cells / (kms * 1e-3) / 1e12 / FP64_PEAK_TFLOPS,
+                         "peak_source": "tools/ubench_chain.cu on B200: 36.8 TFLOP/s fp64 FMA (profiles/r02a_ubench_chain.txt)"}}
         s2.close()
         # end to end through the host-array entry point: pinned HOST U up, time_step(), U down, every step
         Uh = torch.empty((cfg.nx, cfg.ny, 4), dtype=torch.float32).pin_memory()

@@ -76,6 +76,7 @@ EXPORTS = [
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
     "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len", "b200cfd_poisson_change_ptr",
     "b200cfd_set_step_global", "b200cfd_pack_columns", "b200cfd_unpack_columns",
+    "b200cfd_step_splits", "b200cfd_step_part", "b200cfd_halo_rows",
 ]
 
 _lib = None
@@ -131,6 +132,9 @@ def load():
     lib.b200cfd_set_step_global.argtypes = [vp, i64, dbl, dbl, vp]
     lib.b200cfd_pack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
     lib.b200cfd_unpack_columns.argtypes = [vp, vp, i32, i32, vp, vp]
+    lib.b200cfd_step_splits.argtypes = [vp]
+    lib.b200cfd_step_part.argtypes = [vp, i32, i32, vp]
+    lib.b200cfd_halo_rows.argtypes = [vp, i32, C.POINTER(vp), i32, i32, i32, vp, i32, i32, vp, vp]
     # ---- include/b200cfd_euler.h ----
     lib.b200cfd_euler_last_error.restype = C.c_char_p
     lib.b200cfd_euler_last_error.argtypes = [vp]

@@ -56,6 +56,8 @@ struct b200cfd_handle {
     cudaStream_t cap_stream = nullptr;
     cudaGraphExec_t step_graph = nullptr;
     cudaGraphExec_t begin_graph = nullptr;   // the step without its closing kernel (multi-GPU: all_gather in between)
+    cudaGraphExec_t part_graph[2] = {nullptr, nullptr};   // x-slabs: the step up to the finalize of the edge columns / the rest
+    int req_halo_l = 0, req_halo_r = 0;      // the halo widths every slab of this decomposition uses (b200cfd_required_halo)
     PoissonTB* tb = nullptr;          // temporally blocked Poisson state (tensor maps, scratch)
     bool last_poisson_tb = false;     // the last b200cfd_poisson call ran through the temporally blocked kernel
     int gpu_launches = 0;             // kernels enqueued by the last b200cfd_step call (per step)
@@ -139,6 +141,7 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     h->cp.n_cells_global = (double)cfg->ny * (double)nxg;
     if (cfg->use_les) { CUC(cudaMalloc(&h->nut_part, NUT_PARTS * sizeof(double))); CUC(cudaMemset(h->nut_part, 0, NUT_PARTS * sizeof(double))); }
     h->clean = clean_plan(h->g, cfg->dtype, h->n_sm);
+    if (cfg->nranks > 1) b200cfd_required_halo(cfg, &h->req_halo_l, &h->req_halo_r);
     const size_t n = (size_t)cfg->ny * cfg->nx, fb = n * h->es;
     CUC(cudaMalloc(&h->ctl, sizeof(StepCtl)));
     CUC(cudaMemset(h->ctl, 0, sizeof(StepCtl)));
@@ -172,6 +175,7 @@ int b200cfd_destroy(b200cfd_handle* h) {
     cudaSetDevice(h->device);
     if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
     if (h->begin_graph) cudaGraphExecDestroy(h->begin_graph);
+    for (cudaGraphExec_t ge : h->part_graph) if (ge) cudaGraphExecDestroy(ge);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     if (h->tb) poisson_tb_destroy(h->tb);
     cudaFree(h->ctl); cudaFree(h->ring); cudaFree(h->ua); cudaFree(h->va); cudaFree(h->ub); cudaFree(h->vb); cudaFree(h->nut_part); cudaFree(h->psi[0]); cudaFree(h->psi[1]);
@@ -206,6 +210,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
     }
     if (h->step_graph) { cudaGraphExecDestroy(h->step_graph); h->step_graph = nullptr; }
     if (h->begin_graph) { cudaGraphExecDestroy(h->begin_graph); h->begin_graph = nullptr; }
+    for (cudaGraphExec_t& ge : h->part_graph) if (ge) { cudaGraphExecDestroy(ge); ge = nullptr; }
     return B200CFD_OK;
 }
 
@@ -346,11 +351,33 @@ static void prof_mark(b200cfd_handle* h, const char* name, cudaStream_t s, int& 
     ++idx;
 }
 
-static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
+// does the step of this handle split into "up to the finalize of the edge columns" + "the rest" (x-slab overlap)?
+static bool step_splits(const b200cfd_handle* h) {
+    const b200cfd_config& c = h->cfg;
+    return h->fast && !h->fin_tma && !h->fuse_apply && c.cleandiv_mode == B200CFD_CLEANDIV_LEXICOGRAPHIC && c.clean_iters > 0 && c.nranks > 1 &&
+           c.poisson_mode == B200CFD_POISSON_AS_EXECUTED && c.omega == 1.0;
+}
+
+// part 0: the whole step.  part 1 / 2 (step_splits only): the step up to and including the finalize of the column blocks
+// at the slab's edges / the finalize of the other column blocks + the closing reduction.
+static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true, int part = 0) {
     const b200cfd_config& c = h->cfg;
     const int dt = c.dtype;
     int nl = 0, pi = 0, close_rb1 = 0;
     const void* nut = nullptr;
+    // columns whose finalize result the halo exchange needs (sent to a neighbour) or overwrites (this slab's halos)
+    const int c_left = c.rank > 0 ? h->g.own0 + h->req_halo_r : 0;
+    const int c_right = c.rank < c.nranks - 1 ? h->g.own1 - h->req_halo_l : h->g.nx;
+    if (part == 2) {
+        // the psi pointers of the fused-correction path are fixed: sweep 1 -> psi[0], sweep 2 -> psi[1]
+        const bool two = h->fuse_corr && c.clean_iters == 2 && clean_sweep_tma_ok(dt, h->g, h->clean, h->ua, h->va, h->psi[0], h->psi[1]);
+        void* last_psi = two ? h->psi[1] : h->psi[(c.clean_iters - 1) & 1];
+        launch_finalize_fast(dt, h->g, h->phys, h->ctl, h->ua, h->va, last_psi, two ? h->psi[0] : nullptr, h->u, h->v, h->ibm, h->mask,
+                             h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s, 2, c_left, c_right);
+        close_rb1 = (h->fuse_k23 ? 1 : 0);
+        launch_ctl_reduce_local(h->ctl, h->ke_part, h->cnt_part, h->n_part_used, h->red, close_rb1, c.pressure_tolerance, h->nut_part, s);
+        return 2;
+    }
     prof_mark(h, nullptr, s, pi);
     if (c.use_les) {
         launch_smagorinsky(dt, h->g, h->u, h->v, h->nu_t, c.cs, s);
@@ -381,6 +408,12 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true) {
     nl += enqueue_clean(h, h->ua, h->va, c.clean_iters, c.cleandiv_mode, s, &last_psi, true, defer, defer ? &fu : nullptr, defer ? &fv : nullptr,
                         defer ? &first_psi : nullptr);
     if (c.cleandiv_mode != B200CFD_CLEANDIV_LEXICOGRAPHIC) prof_mark(h, "clean_divergence", s, pi);
+    if (part == 1) {
+        // edge column blocks only; the rest of the finalize and the closing reduction are part 2
+        launch_finalize_fast(dt, h->g, h->phys, h->ctl, fu, fv, defer ? last_psi : nullptr, defer ? first_psi : nullptr, h->u, h->v, h->ibm, h->mask,
+                             h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s, 1, c_left, c_right);
+        return nl + 1;
+    }
     if (h->fin_tma && defer && last_psi) {
         if (!launch_finalize_tma(dt, h->g, h->phys, h->ctl, fu, fv, last_psi, first_psi, h->u, h->v, h->ibm, h->mask, h->y, h->ke_part, h->cnt_part, h->flags, h->n_sm, s))
             h->err = "launch of the TMA finalize kernel failed";
@@ -458,6 +491,53 @@ int b200cfd_step_begin(b200cfd_handle* h, int use_graph, void* stream) {
     }
     return B200CFD_OK;
 }
+// x-slab overlap: part 1 = the step up to the finalize of the column blocks at the slab's edges (the halo columns and the
+// owned columns the neighbours need); the caller can then start the halo exchange on another stream while part 2 (the
+// finalize of all the other column blocks + this slab's reduction vector) runs.  Returns B200CFD_ESTATE when the step
+// of this handle does not split (general kernels): use b200cfd_step_begin then.
+int b200cfd_step_part(b200cfd_handle* h, int part, int use_graph, void* stream) {
+    if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");
+    if (part != 1 && part != 2) return fail(h, B200CFD_EINVAL, "part must be 1 or 2");
+    if (!step_splits(h)) return fail(h, B200CFD_ESTATE, "the step of this handle does not split (b200cfd_step_splits)");
+    cudaStream_t s = (cudaStream_t)stream;
+    CU(h, cudaSetDevice(h->device));
+    cudaGraphExec_t& ge = h->part_graph[part - 1];
+    if (use_graph) {
+        if (!ge) {
+            cudaGraph_t graph = nullptr;
+            CU(h, cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+            const int n = enqueue_step(h, h->cap_stream, false, part);
+            if (part == 1) h->gpu_launches = n + 3;          // + finalize of the other blocks, the local reduction, the closing kernel
+            cudaError_t e = cudaStreamEndCapture(h->cap_stream, &graph);
+            if (e != cudaSuccess) return fail(h, B200CFD_ECUDA, "graph capture: %s", cudaGetErrorString(e));
+            e = cudaGraphInstantiate(&ge, graph, 0);
+            cudaGraphDestroy(graph);
+            if (e != cudaSuccess) { ge = nullptr; return fail(h, B200CFD_ECUDA, "graph instantiate: %s", cudaGetErrorString(e)); }
+        }
+        CU(h, cudaGraphLaunch(ge, s));
+    } else {
+        const int n = enqueue_step(h, s, false, part);
+        if (part == 1) h->gpu_launches = n + 3;
+        CHECK_LAUNCH(h);
+    }
+    return B200CFD_OK;
+}
+int b200cfd_step_splits(b200cfd_handle* h) { return (h && h->bound && step_splits(h)) ? 1 : 0; }
+
+// All fields (nfields <= 4) and both sides of a halo refresh in one launch.  pack != 0: columns [j_left, j_left+n_left) of
+// every field -> buf_left[nfields][ny][n_left], [j_right, j_right+n_right) -> buf_right[nfields][ny][n_right]; else the inverse.
+int b200cfd_halo_rows(b200cfd_handle* h, int pack, void* const* fields, int nfields, int j_left, int n_left, void* buf_left,
+                      int j_right, int n_right, void* buf_right, void* stream) {
+    if (!h || !fields || nfields < 1 || nfields > 4) return fail(h, B200CFD_EINVAL, "1..4 fields");
+    if (n_left < 0 || n_right < 0 || (n_left > 0 && (!buf_left || j_left < 0 || j_left + n_left > h->g.nx)) ||
+        (n_right > 0 && (!buf_right || j_right < 0 || j_right + n_right > h->g.nx)))
+        return fail(h, B200CFD_EINVAL, "columns outside the slab");
+    CU(h, cudaSetDevice(h->device));
+    launch_halo_rows(h->es, pack != 0, h->g, fields, nfields, j_left, n_left, buf_left, j_right, n_right, buf_right, (cudaStream_t)stream);
+    CHECK_LAUNCH(h);
+    return B200CFD_OK;
+}
+
 int b200cfd_step_end(b200cfd_handle* h, const double* gathered, int nranks, void* stream) {
     if (!h || !h->bound) return fail(h, B200CFD_ESTATE, "bind_fields first");
     if (nranks < 1) return fail(h, B200CFD_EINVAL, "nranks < 1");

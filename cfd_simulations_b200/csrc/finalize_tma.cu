@@ -251,7 +251,12 @@ static FinPlan fin_plan(const Geom& g, int n_sm) {
 }
 
 bool finalize_tma_ok(int dtype, const Geom& g, const void* ua, const void* va, const void* psi, const void* psi1) {
-    static const int on = fin_env("B200CFD_FIN_TMA", 1);
+    // OFF by default - measured on B200 (profiles/r02g_phases.txt): parity-green, but SLOWER than the register-marching
+    // k_finalize_fast (4096x1024: 86 us against 78 us; 16384^2: 4.6 ms against 3.2 ms).  With four staged arrays a warp
+    // needs 24 KB of ring and 220-248 registers, so only 8 warps fit an SM, and a single in-order instruction stream per
+    // warp (1000 instructions per 3 rows, a third of them register moves of the rotated row arrays) cannot hide its own
+    // latencies; the marching kernel runs 12 warps per SM.  B200CFD_FIN_TMA=1 selects this kernel for experiments.
+    static const int on = fin_env("B200CFD_FIN_TMA", 0);
     const int es = dtype == 0 ? 8 : 4;
     if (!on || !psi || g.nx % 4 || g.nx < 8 || (g.pitch * es) % 16) return false;
     if (((uintptr_t)ua | (uintptr_t)va | (uintptr_t)psi | (uintptr_t)psi1) & 15) return false;

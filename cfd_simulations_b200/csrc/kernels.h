@@ -64,6 +64,9 @@ void launch_ctl_end_step(StepCtl* ctl, const CtlParams& cp, const double* gather
 // ---- x-slab halos: strided columns <-> contiguous buffer [ny][ncols] (halo.cu) -------------------
 void launch_pack_columns(int es, const Geom& g, const void* field, int j0, int ncols, void* buf, cudaStream_t s);
 void launch_unpack_columns(int es, const Geom& g, void* field, int j0, int ncols, const void* buf, cudaStream_t s);
+// all fields (nf <= 4) and both sides in ONE launch: columns [jl, jl+nl) <-> bl[nf][ny][nl], [jr, jr+nr) <-> br[nf][ny][nr]
+void launch_halo_rows(int es, bool pack, const Geom& g, void* const* fields, int nf, int jl, int nl, void* bl, int jr, int nr,
+                      void* br, cudaStream_t s);
 void launch_health(int dtype, const Geom& g, const void* u, const void* v, unsigned long long* out4, cudaStream_t s);
 void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, StepCtl* ctl, cudaStream_t s);
 
@@ -81,10 +84,13 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
                                  void* div_out, void* ua, void* va, double inv_dt, StepCtl* ctl, const uint8_t* flags,
                                  int n_sm, cudaStream_t s);
 int finalize_fast_num_partials(const Geom& g, int n_sm);
+// part 0: every column block.  x-slabs split the launch so that the halo exchange can start while the bulk of the kernel
+// still runs: part 1 = the column blocks that overlap [0, c_left) or [c_right, nx) (the halo columns and the owned columns
+// the neighbours need), part 2 = all the others.
 void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
                           const void* psi_or_null, const void* psi1_or_null, void* u, void* v, const double* ibm, const uint8_t* mask,
                           const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
-                          int n_sm, cudaStream_t s);
+                          int n_sm, cudaStream_t s, int part = 0, int c_left = 0, int c_right = 0);
 // K5 with its rows staged by TMA (finalize_tma.cu); psi (the last pending correction) is required
 bool finalize_tma_ok(int dtype, const Geom& g, const void* ua, const void* va, const void* psi, const void* psi1);
 int finalize_tma_num_partials(const Geom& g, int n_sm);

@@ -336,12 +336,14 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
                 const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u, T* __restrict__ v,
                 const double* __restrict__ ibm, const uint8_t* __restrict__ mask, const double* __restrict__ y,
                 double* __restrict__ ke_part, unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags,
-                int ntx, int rpb) {
+                int ntx, int rpb, int bx_cut, int bx_off_a, int bx_off_b, int nbx_total) {
     constexpr bool PSI = NPSI > 0;
     pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
-    const int own_c0 = blockIdx.x * FB_OWN + warp * FW_OWN;        // first column owned by this warp
+    // column block of this CUDA block: a launch may cover a subset of the column blocks (x-slab edge / interior split)
+    const int bx = (int)blockIdx.x < bx_cut ? (int)blockIdx.x + bx_off_a : (int)blockIdx.x + bx_off_b;
+    const int own_c0 = bx * FB_OWN + warp * FW_OWN;                // first column owned by this warp
     const int c0 = own_c0 - 2 + 2 * lane;                          // this lane's two columns: c0, c0+1
     const bool inb = c0 >= 0 && c0 + 1 < g.nx;
     const bool owner = inb && lane >= 1 && lane <= 30;
@@ -504,7 +506,7 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
             }
         }
     }
-    finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * gridDim.x + blockIdx.x);
+    finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * nbx_total + bx);
 }
 
 void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
@@ -538,12 +540,21 @@ int finalize_fast_num_partials(const Geom& g, int n_sm) {
 void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl, const void* ua, const void* va,
                           const void* psi, const void* psi1, void* u, void* v, const double* ibm, const uint8_t* mask,
                           const double* y, double* ke_partials, unsigned long long* cnt_partials, const uint8_t* flags,
-                          int n_sm, cudaStream_t s) {
+                          int n_sm, cudaStream_t s, int part, int c_left, int c_right) {
     int rpb;
-    const dim3 grid = finalize_fast_grid(g, n_sm, &rpb);
+    dim3 grid = finalize_fast_grid(g, n_sm, &rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
     const int np = psi ? (psi1 ? 2 : 1) : 0;
-#define FF(T, NP) launch_pdl(k_finalize_fast<T, NP>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (const T*)psi1, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb)
+    const int nbx = (int)grid.x;
+    // column blocks [0, bl) overlap [0, c_left); column blocks [br, nbx) overlap [c_right, nx)
+    int bl = part ? (c_left + FB_OWN - 1) / FB_OWN : 0, br = part ? c_right / FB_OWN : nbx;
+    if (bl > nbx) bl = nbx;
+    if (br < bl) br = bl;
+    int cut = nbx, off_a = 0, off_b = 0;
+    if (part == 1) { grid.x = bl + (nbx - br); cut = bl; off_a = 0; off_b = br - bl; }        // edges: [0, bl) and [br, nbx)
+    else if (part == 2) { grid.x = br - bl; cut = nbx; off_a = bl; }                            // interior: [bl, br)
+    if (grid.x == 0) return;
+#define FF(T, NP) launch_pdl(k_finalize_fast<T, NP>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (const T*)psi1, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb, cut, off_a, off_b, nbx)
     if (dtype == 0) { if (np == 2) FF(double, 2); else if (np == 1) FF(double, 1); else FF(double, 0); }
     else { if (np == 2) FF(float, 2); else if (np == 1) FF(float, 1); else FF(float, 0); }
 #undef FF

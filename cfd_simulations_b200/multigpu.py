@@ -77,15 +77,20 @@ class HaloExchanger:
     pack(field, j0, ncols, out2d) / unpack(field, j0, ncols, in2d) move field[:, j0:j0+ncols] to / from a contiguous
     (ny, ncols) buffer; buffers are allocated once with `alloc(shape)` on the device the backend communicates from."""
 
-    def __init__(self, plan: SlabPlan, ny, nfields, alloc, pack, unpack, group=None):
+    def __init__(self, plan: SlabPlan, ny, nfields, alloc, pack, unpack, group=None, halo_rows=None):
+        """halo_rows(pack: bool, fields, j_left, n_left, buf_left, j_right, n_right, buf_right): optional fused kernel that
+        moves all fields and both sides in one launch (the product passes b200cfd_halo_rows); without it pack / unpack are
+        called once per field and side."""
         self.plan, self.ny, self.nf, self.pack, self.unpack, self.group = plan, ny, nfields, pack, unpack, group
+        self.halo_rows = halo_rows
         p = plan
         mk = lambda n: alloc((nfields, ny, n)) if n > 0 else None
         self.sbuf_l, self.sbuf_r = mk(p.send_left), mk(p.send_right)
         self.rbuf_l, self.rbuf_r = mk(p.halo_left), mk(p.halo_right)
         self.bytes_per_exchange = sum(b.numel() * b.element_size() for b in (self.sbuf_l, self.sbuf_r) if b is not None)
         # pack launches for the sides that send + unpack launches for the sides that receive, per field
-        self.launches_per_exchange = nfields * sum(b is not None for b in (self.sbuf_l, self.sbuf_r, self.rbuf_l, self.rbuf_r))
+        self.launches_per_exchange = (2 if halo_rows is not None else
+                                      nfields * sum(b is not None for b in (self.sbuf_l, self.sbuf_r, self.rbuf_l, self.rbuf_r)))
 
     def exchange(self, fields, marks=None):
         """marks: optional list that receives 4 CUDA events (before pack, after pack, after send/recv, after unpack)."""
@@ -103,11 +108,14 @@ class HaloExchanger:
             ops.append(dist.P2POp(dist.irecv, self.rbuf_l, p.rank - 1, self.group))
         if self.rbuf_r is not None:
             ops.append(dist.P2POp(dist.irecv, self.rbuf_r, p.rank + 1, self.group))
-        for k, f in enumerate(fields):
-            if self.sbuf_l is not None:
-                self.pack(f, p.own0, p.send_left, self.sbuf_l[k])
-            if self.sbuf_r is not None:
-                self.pack(f, p.own1 - p.send_right, p.send_right, self.sbuf_r[k])
+        if self.halo_rows is not None:
+            self.halo_rows(True, fields, p.own0, p.send_left, self.sbuf_l, p.own1 - p.send_right, p.send_right, self.sbuf_r)
+        else:
+            for k, f in enumerate(fields):
+                if self.sbuf_l is not None:
+                    self.pack(f, p.own0, p.send_left, self.sbuf_l[k])
+                if self.sbuf_r is not None:
+                    self.pack(f, p.own1 - p.send_right, p.send_right, self.sbuf_r[k])
         if self.sbuf_l is not None:
             ops.append(dist.P2POp(dist.isend, self.sbuf_l, p.rank - 1, self.group))
         if self.sbuf_r is not None:
@@ -118,11 +126,14 @@ class HaloExchanger:
         for w in dist.batch_isend_irecv(ops):
             w.wait()
         mark()
-        for k, f in enumerate(fields):
-            if self.rbuf_l is not None:
-                self.unpack(f, 0, p.halo_left, self.rbuf_l[k])
-            if self.rbuf_r is not None:
-                self.unpack(f, p.own1, p.halo_right, self.rbuf_r[k])
+        if self.halo_rows is not None:
+            self.halo_rows(False, fields, 0, p.halo_left, self.rbuf_l, p.own1, p.halo_right, self.rbuf_r)
+        else:
+            for k, f in enumerate(fields):
+                if self.rbuf_l is not None:
+                    self.unpack(f, 0, p.halo_left, self.rbuf_l[k])
+                if self.rbuf_r is not None:
+                    self.unpack(f, p.own1, p.halo_right, self.rbuf_r[k])
         mark()
 
 

@@ -87,9 +87,25 @@ class SnapshotWriter:
             f: Future = Future()
             f.set_result(group_name(step))
             return f
+        nranks = getattr(solver, "_nranks", 1)
         X, Y = getattr(solver, "X", None), getattr(solver, "Y", None)
-        grids = {"X": None if X is None else np.asarray(X), "Y": None if Y is None else np.asarray(Y)}
-        if hasattr(solver, "device_tensor") and getattr(solver, "_nranks", 1) == 1:
+        if X is None or Y is None or nranks > 1:
+            # solvers set up on the device keep no host grid, and a slab only knows its own columns: the file holds the
+            # GLOBAL grid of the reference layout (v5.py:269-272)
+            cfg = solver.config
+            X, Y = np.meshgrid(np.linspace(cfg.x_min, cfg.x_max, cfg.nx), np.linspace(cfg.y_min, cfg.y_max, cfg.ny))
+        grids = {"X": np.asarray(X), "Y": np.asarray(Y)}
+        if nranks > 1:
+            # x-slabs: every rank calls this; the owned columns of u, v and of the (device-computed) vorticity are gathered
+            # and rank 0 alone writes the global field.  The other ranks get an already resolved Future.
+            w = solver.compute_vorticity_device()
+            arrays = {"u": solver.gather_to_root("u"), "v": solver.gather_to_root("v"), "vorticity": solver.gather_to_root(w)}
+            if getattr(solver, "_rank", 0) == 0:
+                fut = self.executor.submit(self._write, step, current_time, arrays, grids)
+            else:
+                fut = Future()
+                fut.set_result(group_name(step))
+        elif hasattr(solver, "device_tensor"):
             fut = self._save_device(solver, step, current_time, grids)
         else:
             arrays = {"u": np.array(solver.u), "v": np.array(solver.v), "vorticity": np.array(solver.compute_vorticity())}

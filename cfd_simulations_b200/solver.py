@@ -8,6 +8,7 @@ There is no CPU fallback: constructing a solver without the CUDA library / a CUD
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -123,7 +124,12 @@ class OptimizedTurbulentSolver:
                 plan, cfg.ny, 2, alloc=lambda shape: torch.empty(shape, dtype=tdt, device=dev),
                 pack=lambda f, j0, n, out: check(lib.b200cfd_pack_columns(h, f.data_ptr(), j0, n, out.data_ptr(), sp()), h),
                 unpack=lambda f, j0, n, src: check(lib.b200cfd_unpack_columns(h, f.data_ptr(), j0, n, src.data_ptr(), sp()), h),
-                group=group)
+                group=group, halo_rows=self._halo_rows)
+            # halo exchange off the compute stream: its own stream, ordered against the step by events
+            self._comm_stream = torch.cuda.Stream(device=dev)
+            self._ev_edges = torch.cuda.Event()
+            self._ev_halo = torch.cuda.Event()
+            self._overlap = bool(lib.b200cfd_step_splits(self._h)) and not bool(os.environ.get("B200CFD_NO_OVERLAP"))
         torch.cuda.synchronize(dev)
 
     # ---- lifetime ----
@@ -209,18 +215,42 @@ class OptimizedTurbulentSolver:
             self._step += m
             done += m
 
+    def _halo_rows(self, pack, fields, jl, nl, bl, jr, nr, br):
+        """All fields and both sides of a halo refresh in one launch (b200cfd_halo_rows) on the current stream."""
+        ptrs = (C.c_void_p * len(fields))(*[f.data_ptr() for f in fields])
+        check(self._lib.b200cfd_halo_rows(self._h, int(bool(pack)), ptrs, len(fields), int(jl), int(nl if bl is not None else 0),
+                                          bl.data_ptr() if bl is not None else None, int(jr), int(nr if br is not None else 0),
+                                          br.data_ptr() if br is not None else None, _stream_ptr(self.device)), self._h)
+
     def _advance_slabs(self, n_steps, cap):
-        """Slab stepping: per step one all_gather of the reduction vector and one halo refresh of u, v."""
+        """Slab stepping.  Per step: one all_gather of the 128-byte reduction vector and one halo refresh of u, v.  When the
+        step splits (fast kernels), the refresh runs on its own stream and overlaps with the bulk of the finalize kernel:
+          compute stream: part 1 (... finalize of the edge columns) | part 2 (finalize of the rest, local reduction) |
+                          all_gather | closing kernel | wait for the halos
+          comm stream:                 wait part 1 | pack (1 launch) | NCCL send/recv | unpack (1 launch)"""
         import torch.distributed as dist
         lib, h, sp = self._lib, self._h, lambda: _stream_ptr(self.device)
         u, v = self._d["u"], self._d["v"]
+        main = torch.cuda.current_stream(self.device)
         for _ in range(n_steps):
             if self._step - self._fetched >= cap:
                 self._sync_scalars()
-            check(lib.b200cfd_step_begin(h, int(self._use_graph), sp()), h)
-            dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
-            check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
-            self._halo.exchange([u, v])
+            if self._overlap:
+                check(lib.b200cfd_step_part(h, 1, int(self._use_graph), sp()), h)
+                self._ev_edges.record(main)
+                with torch.cuda.stream(self._comm_stream):
+                    self._comm_stream.wait_event(self._ev_edges)
+                    self._halo.exchange([u, v])
+                    self._ev_halo.record(self._comm_stream)
+                check(lib.b200cfd_step_part(h, 2, int(self._use_graph), sp()), h)
+                dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+                check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+                main.wait_event(self._ev_halo)
+            else:
+                check(lib.b200cfd_step_begin(h, int(self._use_graph), sp()), h)
+                dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+                check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+                self._halo.exchange([u, v])
             self._step += 1
 
     def gather(self, name):
@@ -397,12 +427,29 @@ class OptimizedTurbulentSolver:
         return 0.5 * (u ** 2 + v ** 2)
 
     def compute_vorticity(self):
+        """v5.py:365-373 on the LOCAL array (host copy).  Solvers set up on the device (setup="device") hold no host
+        mask: the device kernel (same formula, NaN inside the cylinder) is used instead."""
+        if self.cylinder_mask is None:
+            return self.compute_vorticity_device().cpu().numpy()
         cfg = self.config
         u, v = self.u, self.v
         w = np.zeros_like(u)
         w[1:-1, 1:-1] = (v[1:-1, 2:] - v[1:-1, :-2]) / (2 * cfg.dx) - (u[2:, 1:-1] - u[:-2, 1:-1]) / (2 * cfg.dy)
         w[self.cylinder_mask] = np.nan
         return w
+
+    def gather_to_root(self, array_or_name, root=0):
+        """Global (ny, nx) host array assembled on rank `root` from the OWNED columns of every slab (None on the other
+        ranks).  `array_or_name`: a field name or a LOCAL (ny, nx_local) array / CUDA tensor (e.g. the device vorticity)."""
+        a = self._get(array_or_name) if isinstance(array_or_name, str) else (
+            array_or_name.cpu().numpy() if isinstance(array_or_name, torch.Tensor) else np.asarray(array_or_name))
+        loc = np.ascontiguousarray(a[:, self.plan.own0:self.plan.own1])
+        if self._nranks == 1:
+            return loc
+        import torch.distributed as dist
+        parts = [None] * self._nranks if self._rank == root else None
+        dist.gather_object(loc, parts, dst=root, group=self._group)
+        return np.concatenate(parts, axis=1) if self._rank == root else None
 
     def compute_vorticity_device(self, out=None):
         """compute_vorticity (v5.py:365-373) on the device: a CUDA tensor (NaN inside the cylinder), nothing crosses PCIe."""
@@ -452,6 +499,8 @@ class OptimizedTurbulentSolver:
         lib, h, sp = self._lib, self._h, lambda: _stream_ptr(self.device)
         u, v = self._d["u"], self._d["v"]
         ev = lambda: torch.cuda.Event(enable_timing=True)
+        if self._overlap:
+            return self._profile_overlapped(n_steps)
         check(lib.b200cfd_profile_begin(h), h)
         marks, halo_marks = [], []
         for _ in range(n_steps):
@@ -484,6 +533,65 @@ class OptimizedTurbulentSolver:
                         "halo_unpack": round(hmean(2, 3), 5)})
         return out
 
+    def _profile_overlapped(self, n_steps):
+        """The overlapped slab step (graph replay, as timed): CUDA events on both streams.  `exposed_*` are the parts of the
+        step that are NOT hidden behind compute: what the compute stream spends in the all_gather + closing kernel, and how
+        long it then still waits for the halos."""
+        import torch.distributed as dist
+        lib, h, sp = self._lib, self._h, lambda: _stream_ptr(self.device)
+        u, v = self._d["u"], self._d["v"]
+        main = torch.cuda.current_stream(self.device)
+        ev = lambda: torch.cuda.Event(enable_timing=True)
+        recs = []
+        for _ in range(n_steps):
+            e = [ev() for _ in range(6)]
+            hm = []
+            e[0].record(main)
+            check(lib.b200cfd_step_part(h, 1, int(self._use_graph), sp()), h)
+            e[1].record(main)
+            with torch.cuda.stream(self._comm_stream):
+                self._comm_stream.wait_event(e[1])
+                self._halo.exchange([u, v], marks=hm)
+                self._ev_halo.record(self._comm_stream)
+            check(lib.b200cfd_step_part(h, 2, int(self._use_graph), sp()), h)
+            e[2].record(main)
+            dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+            e[3].record(main)
+            check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+            e[4].record(main)
+            main.wait_event(self._ev_halo)
+            e[5].record(main)
+            recs.append((e, hm))
+            self._step += 1
+        torch.cuda.synchronize(self.device)
+        mean = lambda f: round(sum(f(e, hm) for e, hm in recs) / len(recs), 5)
+        out = {"overlap": True,
+               "part1_to_edge_finalize": mean(lambda e, hm: e[0].elapsed_time(e[1])),
+               "part2_rest_of_finalize": mean(lambda e, hm: e[1].elapsed_time(e[2])),
+               "exposed_all_gather": mean(lambda e, hm: e[2].elapsed_time(e[3])),
+               "exposed_step_end": mean(lambda e, hm: e[3].elapsed_time(e[4])),
+               "exposed_wait_for_halos": mean(lambda e, hm: e[4].elapsed_time(e[5])),
+               "step_total": mean(lambda e, hm: e[0].elapsed_time(e[5]))}
+        if recs and len(recs[0][1]) == 4:
+            out.update({"comm_stream_halo_pack": mean(lambda e, hm: hm[0].elapsed_time(hm[1])),
+                        "comm_stream_halo_send_recv": mean(lambda e, hm: hm[1].elapsed_time(hm[2])),
+                        "comm_stream_halo_unpack": mean(lambda e, hm: hm[2].elapsed_time(hm[3]))})
+        # per-kernel times of the same step come from the unsplit stream-launch profile (b200cfd_profile_*)
+        check(lib.b200cfd_profile_begin(h), h)
+        for _ in range(min(n_steps, 3)):
+            check(lib.b200cfd_step_begin(h, 0, sp()), h)
+            dist.all_gather_into_tensor(self._gathered.view(-1), self._red, group=self._group)
+            check(lib.b200cfd_step_end(h, self._gathered.data_ptr(), self._nranks, sp()), h)
+            self._halo.exchange([u, v])
+            self._step += 1
+        names = C.create_string_buffer(1024)
+        ms = (C.c_double * 32)()
+        n = lib.b200cfd_profile_end(h, names, 1024, ms, 32)
+        if n < 0:
+            check(n, h)
+        out["kernels"] = dict(zip(names.value.decode().split(";"), [round(x, 5) for x in list(ms)[:n]]))
+        return out
+
     # ---- introspection ----
     def launches_per_step(self):
         return int(self._lib.b200cfd_launches_per_step(self._h))
@@ -494,7 +602,8 @@ class OptimizedTurbulentSolver:
         return n + (self._halo.launches_per_exchange if self._halo is not None else 0)
 
     def collectives_per_step(self):
-        return "1 all_gather (128 B per rank) + 1 batched NCCL send/recv of the u, v halo columns"
+        return ("1 all_gather (128 B per rank) + 1 batched NCCL send/recv of the u, v halo columns" +
+                (" on a communication stream, overlapped with the finalize kernel" if getattr(self, "_overlap", False) else ""))
 
     def clean_plan(self):
         out = (C.c_int * 8)()

@@ -116,6 +116,16 @@ int b200cfd_step_host(b200cfd_handle* h, void* u_host, void* v_host, int n_steps
 int   b200cfd_required_halo(const b200cfd_config* cfg, int* left, int* right);
 int   b200cfd_step_begin(b200cfd_handle* h, int use_graph, void* stream);
 int   b200cfd_step_end(b200cfd_handle* h, const double* gathered_dev, int nranks, void* stream);
+/* Overlap of the halo exchange with the tail of the step: when b200cfd_step_splits(h) is 1, step_begin
+ * can be issued in two parts.  part 1 = the step up to the finalize of the column blocks at the slab's edges (its halo
+ * columns and the owned columns its neighbours need); after it the caller starts b200cfd_halo_rows(pack) -> NCCL
+ * send/recv -> b200cfd_halo_rows(unpack) on a communication stream, while part 2 (the finalize of every other column
+ * block + this slab's reduction vector) runs on the compute stream. */
+int   b200cfd_step_splits(b200cfd_handle* h);
+int   b200cfd_step_part(b200cfd_handle* h, int part, int use_graph, void* stream);
+/* All fields (1..4) and both sides of a halo refresh in ONE launch (replaces 2 x nfields pack_columns calls). */
+int   b200cfd_halo_rows(b200cfd_handle* h, int pack, void* const* fields, int nfields, int j_left, int n_left, void* buf_left,
+                        int j_right, int n_right, void* buf_right, void* stream);
 void* b200cfd_reduction_ptr(b200cfd_handle* h);
 /* Device address of one double: max|dphi| over the OWNED cells of the last completed red-black iteration of
  * b200cfd_poisson (the reference's max_change, v5.py:212-225).  The slab Poisson solve all-reduces (MAX) it over the ranks

@@ -114,3 +114,26 @@ def test_long_run_drag_lift_probe_match_oracle_series():
     a = strouhal(out["t"], out["vprobe"], cfg, t_discard=5.0)
     b = strouhal(g["t"][:n], g["vprobe"][:n], cfg, t_discard=5.0)
     assert abs(a["St"] - b["St"]) <= 5e-3 * abs(b["St"])
+
+
+def test_snapshot_of_device_setup_solver(tmp_path):
+    """setup="device" keeps no host mask / grid: the snapshot must still hold the device vorticity (NaN only inside the
+    cylinder) and the global X, Y of the reference layout (v5.py:454-470)."""
+    from cfd_simulations_b200.snapshot import SnapshotWriter, load_snapshot
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg = _cfg(tmp_path)
+    a = OptimizedTurbulentSolver(cfg, setup="device")
+    b = OptimizedTurbulentSolver(cfg)
+    a.advance(7); b.advance(7)
+    assert a.cylinder_mask is None
+    wa = a.compute_vorticity()
+    wb = b.compute_vorticity()
+    assert np.array_equal(np.isnan(wa), np.isnan(wb)) and 0 < np.isnan(wa).sum() < wa.size // 4
+    with SnapshotWriter(cfg, backend="npz") as w:
+        w.save_data_to_hdf5(a, 7, 1.4e-4).result()
+        s = load_snapshot(w.path, 7)
+    assert s["X"].shape == (cfg.ny, cfg.nx) and s["Y"].shape == (cfg.ny, cfg.nx)
+    assert np.allclose(s["X"][0], np.linspace(cfg.x_min, cfg.x_max, cfg.nx)) and np.array_equal(np.isnan(s["vorticity"]), np.isnan(wb))
+    ok = ~np.isnan(wb)
+    assert np.abs(s["vorticity"][ok] - wb[ok]).max() <= 1e-6 * np.abs(wb[ok]).max()   # device setup: transcendental ulps
+    a.close(); b.close()

@@ -121,6 +121,17 @@ def _nccl_worker(rank, world, port, out):
         s.advance(15)
         res = {k: s.gather(k) for k in ("u", "v", "phi")}
         s._sync_scalars()
+        # snapshot of a slab-decomposed solver: every rank calls the writer, rank 0 alone writes the GLOBAL field
+        import tempfile
+        from cfd_simulations_b200.snapshot import SnapshotWriter, load_snapshot
+        snap_dir = out["snap_dir"]
+        cfg_s = _cfg(1600, 128)
+        cfg_s.output_dir, cfg_s.hdf5_file = snap_dir, "slabs.h5"
+        with SnapshotWriter(cfg_s, backend="npz") as w:
+            w.save_data_to_hdf5(s, 15, 3e-4).result()
+            dist.barrier()
+            if rank == 0:
+                out["snapshot"] = load_snapshot(w.path, 15)
         # iterative Poisson on the slabs: NCCL halo refresh + all_reduce(MAX) of the per-iteration change
         _, div = _poisson_case(1600, 128)
         p = s.plan
@@ -155,6 +166,8 @@ def test_nccl_slabs_match_single_gpu():
     _, div = _poisson_case(1600, 128)
     single = lambda iters, tol: ref.solve_pressure_fast(div, mode="as_written", max_iter=iters, tol=tol, omega=1.0,
                                                         temporal_depth=1, return_info=True)
+    import tempfile
+    out["snap_dir"] = tempfile.mkdtemp(prefix="b200cfd_slab_snap_")
     out["tol"] = 0.5 * (single(37, 0.0)[2] + single(38, 0.0)[2])
     pf = single(23, 0.0)
     pt = single(5000, float(out["tol"]))
@@ -173,6 +186,13 @@ def test_nccl_slabs_match_single_gpu():
     one.advance(15)
     for k, a in out["fields"].items():
         assert rel_l2(a, getattr(one, k)) <= 1e-13, k
+    snap = out["snapshot"]
+    assert snap["u"].shape == (128, 1600) and snap["X"].shape == (128, 1600)
+    assert rel_l2(snap["u"], one.u) <= 1e-13 and rel_l2(snap["v"], one.v) <= 1e-13
+    w1 = one.compute_vorticity()
+    ok = ~np.isnan(w1)
+    assert np.array_equal(np.isnan(snap["vorticity"]), ~ok)
+    assert np.abs(snap["vorticity"][ok] - w1[ok]).max() <= 1e-10 * np.abs(w1[ok]).max()
     one._sync_scalars()
     for key in ("dt", "max_div_post", "mean_energy", "max_vorticity"):
         assert abs(out["scalars"][key] - one.scalars[-1][key]) <= 1e-12 * abs(one.scalars[-1][key])

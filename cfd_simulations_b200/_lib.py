@@ -36,6 +36,7 @@ class Config(C.Structure):
         ("pressure_tolerance", C.c_double), ("omega", C.c_double),
         ("rank", C.c_int32), ("nranks", C.c_int32), ("nx_global", C.c_int32), ("x_offset", C.c_int32),
         ("halo_left", C.c_int32), ("halo_right", C.c_int32),
+        ("pert_amplitude", C.c_double), ("scalar_f32", C.c_int32), ("variant_set", C.c_int32),
     ]
 
 

@@ -47,14 +47,22 @@ class OptimizedTurbulentConfig:
     output_dir: str = "v5_re_600"
     hdf5_file: str = "v5_re_600.h5"
     dpi: int = 200
+    # --- not in the reference's dataclass: select the v3 / v4 variants of the same step ---
+    perturbation_amplitude: float = 0.01    # inflow perturbation: v5.py:351 and v4.py:349 use 0.01, v3.py:329 uses 0.005
+    float32_scalars: bool = True            # v5.py:80-82,321,326 round nu, dt, artificial_viscosity and the step dt to
+                                            # float32; v3 / v4 keep Python floats (v4.py:79-80,319,324)
 
     def __post_init__(self):
         # v5.py:78-83
         self.dx = (self.x_max - self.x_min) / (self.nx - 1)
         self.dy = (self.y_max - self.y_min) / (self.ny - 1)
-        self.nu = np.float32(1.0 / self.Re)
-        self.dt = np.float32(self.dt_base)
-        self.artificial_viscosity = np.float32(self.artificial_viscosity)
+        if self.float32_scalars:
+            self.nu = np.float32(1.0 / self.Re)
+            self.dt = np.float32(self.dt_base)
+            self.artificial_viscosity = np.float32(self.artificial_viscosity)
+        else:                                # v4.py:79-80
+            self.nu = 1.0 / self.Re
+            self.dt = self.dt_base
         self.parallel_threads = min(self.parallel_threads, os.cpu_count() or 1)
 
     @property

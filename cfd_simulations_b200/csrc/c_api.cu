@@ -139,6 +139,9 @@ int b200cfd_create(const b200cfd_config* cfg, int device, b200cfd_handle** out) 
     h->cp.adaptive_dt = cfg->adaptive_dt; h->cp.initial_steps = cfg->initial_steps > 0 ? cfg->initial_steps : 1;
     h->cp.is_f32 = f32; h->cp.use_les = cfg->use_les;
     h->cp.n_cells_global = (double)cfg->ny * (double)nxg;
+    h->cp.pert_amplitude = cfg->variant_set ? cfg->pert_amplitude : 0.01;
+    h->cp.scalar_f32 = cfg->variant_set ? cfg->scalar_f32 : 1;
+    h->cp.pad = 0;
     if (cfg->use_les) { CUC(cudaMalloc(&h->nut_part, NUT_PARTS * sizeof(double))); CUC(cudaMemset(h->nut_part, 0, NUT_PARTS * sizeof(double))); }
     h->clean = clean_plan(h->g, cfg->dtype, h->n_sm);
     if (cfg->nranks > 1) b200cfd_required_halo(cfg, &h->req_halo_l, &h->req_halo_r);
@@ -828,7 +831,7 @@ int b200cfd_k_vorticity(b200cfd_handle* h, const void* u, const void* v, const u
     UNIT_PRE(); launch_vorticity(h->cfg.dtype, h->g, u, v, mask, w, s); UNIT_POST();
 }
 int b200cfd_k_apply_bc(b200cfd_handle* h, void* u, void* v, const double* y, int64_t step, void* stream) {
-    UNIT_PRE(); launch_apply_bc(h->cfg.dtype, h->g, u, v, y, h->cfg.V_inf, h->cfg.y_max, (long long)step, s); UNIT_POST();
+    UNIT_PRE(); launch_apply_bc(h->cfg.dtype, h->g, u, v, y, h->cfg.V_inf, h->cfg.y_max, (long long)step, s, h->cp.pert_amplitude); UNIT_POST();
 }
 int b200cfd_k_apply_ibm(b200cfd_handle* h, void* u, void* v, const double* ibm, double force_strength, void* stream) {
     UNIT_PRE(); launch_apply_ibm(h->cfg.dtype, h->g, u, v, ibm, force_strength, s); UNIT_POST();
@@ -848,7 +851,7 @@ int b200cfd_k_predictor(b200cfd_handle* h, const void* u, const void* v, void* u
     c.dt = dt; c.step = step;
     c.fs = (double)step / (double)h->cp.initial_steps; if (c.fs > 1.0) c.fs = 1.0;
     double sc = (double)step / 1000.0; if (sc > 1.0) sc = 1.0;
-    c.pert_scale = sc * 0.01; c.phase = 0.02 * (double)step;
+    c.pert_scale = sc * h->cp.pert_amplitude; c.phase = 0.02 * (double)step;
     StepCtl* d = nullptr;
     CU(h, cudaMalloc(&d, sizeof(StepCtl)));
     CU(h, cudaMemcpyAsync(d, &c, sizeof c, cudaMemcpyHostToDevice, s));

@@ -17,6 +17,8 @@ struct CtlParams {
     double cfl_target, dt_min, dt_max, dt_base, hmin, nu, av;
     int adaptive_dt, initial_steps, is_f32, use_les;
     double n_cells_global;      // ny * nx_global: denominator of mean(nu_t) (v5.py:323)
+    double pert_amplitude;      // inflow perturbation amplitude (v5 / v4: 0.01, v3: 0.005)
+    int scalar_f32, pad;        // warm-up / adaptive dt rounded to float32 (v5) or kept as doubles (v3 / v4)
 };
 #define NUT_PARTS 256           // fixed number of partial sums of nu_t (deterministic two-stage reduction)
 // sum of nu_t over the OWNED columns into NUT_PARTS partials (LES only; feeds adaptive_time_step's mean(nu_t))
@@ -33,7 +35,7 @@ void launch_divergence(int dtype, const Geom& g, const void* u, const void* v, v
 void launch_gradient(int dtype, const Geom& g, const void* phi, void* gx, void* gy, cudaStream_t s);
 void launch_smagorinsky(int dtype, const Geom& g, const void* u, const void* v, void* nu_t, double cs, cudaStream_t s);
 void launch_apply_bc(int dtype, const Geom& g, void* u, void* v, const double* y, double V_inf, double y_max,
-                     long long step, cudaStream_t s);
+                     long long step, cudaStream_t s, double amplitude = 0.01);
 void launch_apply_ibm(int dtype, const Geom& g, void* u, void* v, const double* ibm, double fs, cudaStream_t s);
 
 // ---- fused step kernels ------------------------------------------------------------------------

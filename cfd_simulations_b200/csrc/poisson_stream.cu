@@ -105,9 +105,10 @@ __global__ void k_stream_make_rhs(int ny, int nx, long long pitch, int jg0, int 
                                   const uint8_t* __restrict__ mask, T* __restrict__ out, uint8_t* __restrict__ tflags,
                                   int OW, int H, int tile_h, int VH, int n_strips, int n_rchunks) {
     const T nan_t = (T)__longlong_as_double(0x7ff8000000000000ll), inf_t = (T)__longlong_as_double(0x7ff0000000000000ll);
-    const long long n = (long long)ny * pitch;
-    for (long long k = blockIdx.x * 256ll + threadIdx.x; k < n; k += (long long)gridDim.x * 256ll) {
-        const int i = (int)(k / pitch), j = (int)(k - (long long)i * pitch), jg = jg0 + j;
+    for (int i = blockIdx.y; i < ny; i += gridDim.y)
+    for (int j = blockIdx.x * 256 + threadIdx.x; j < (int)pitch; j += gridDim.x * 256) {
+        const long long k = (long long)i * pitch + j;
+        const int jg = jg0 + j;
         const bool upd = i >= 1 && i < ny - 1 && j >= 1 && j < nx - 1 && jg >= 1 && jg < nxg - 1;
         const bool msk = mask && mask[k];
         out[k] = !upd ? inf_t : (msk ? nan_t : div[k]);
@@ -291,13 +292,15 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                             const int row = q + j - 1 - lv;                  // row computed by level lv + 1
                             const int off = j - 1 - lv;                      // compile time after unrolling
                             const int back = off >= 0 ? 0 : (-off + SKR - 1) / SKR, jr = off + back * SKR;
-                            double out[SPL];
-                            level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
                             if (lv + 1 < L) {
-#pragma unroll
-                                for (int m = 0; m < SPL; ++m) R[lv + 1][(j + 2) % 3][m] = out[m];
-                            } else if (do_store && st_lane) {
-                                SRow<T>::st(sg + j * P.OW + scol, out);
+                                // the level writes straight into the next level's north row (no copy: the ncu source page
+                                // of the first version showed a quarter of the issue slots going to register moves)
+                                level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW,
+                                      R[lv + 1 < L ? lv + 1 : lv][(j + 2) % 3]);
+                            } else {
+                                double out[SPL];
+                                level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
+                                if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
                             }
                         }
                     }
@@ -427,12 +430,15 @@ static int stream_depth(int L, const CUtensorMap& mi, const CUtensorMap& mr, con
 template <typename T, int MODE>
 static int stream_dispatch(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
                            unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
-    if (MODE == 0) return stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
-    const bool sor = P.omega != 1.0, chk = slots != nullptr;
-    if (sor) return chk ? stream_depth<T, MODE, true, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
-                        : stream_depth<T, MODE, true, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
-    return chk ? stream_depth<T, MODE, false, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
-               : stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    if constexpr (MODE == 0) {
+        return stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    } else {
+        const bool sor = P.omega != 1.0, chk = slots != nullptr;
+        if (sor) return chk ? stream_depth<T, MODE, true, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
+                            : stream_depth<T, MODE, true, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+        return chk ? stream_depth<T, MODE, false, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
+                   : stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+    }
 }
 
 bool poisson_stream_enabled() {
@@ -499,9 +505,11 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     }
     if (cudaMemsetAsync(ps->tflags, 0, ntile, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile flags)"; return -1; }
     const int VH = L + 3;                                           // rows above / below a chunk its pipeline touches
-    if (dtype == 0) k_stream_make_rhs<double><<<nb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
+    const dim3 gnb((unsigned)((g.pitch + 255) / 256), (unsigned)(g.ny < 8192 ? g.ny : 8192));
+    (void)nb;
+    if (dtype == 0) k_stream_make_rhs<double><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
                                                                   ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
-    else k_stream_make_rhs<float><<<nb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const float*)div, mask, (float*)ps->rhs_s,
+    else k_stream_make_rhs<float><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const float*)div, mask, (float*)ps->rhs_s,
                                                     ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
     CUtensorMap m_phi, m_alt, m_rhs, o_phi, o_alt;
     if (!tma_make_2d(&m_phi, dtype, phi, g.nx, g.ny, g.pitch, SW, SKR) || !tma_make_2d(&m_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, SW, SKR) ||

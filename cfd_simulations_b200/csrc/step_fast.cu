@@ -176,6 +176,29 @@ k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __res
     }
 }
 
+// Rows per block of a row-marching kernel from a cost model instead of "about 8 blocks per SM": a launch takes
+// waves x (rows marched per block), waves = ceil(blocks / resident slots), rows marched = rpb + the halo rows a block
+// re-reads + a fixed prologue worth ~6 rows.  At 4096x1024 the old rule gave 2.6-2.8 waves of 8-16-row blocks (the last wave
+// 60-80 % full, 12-25 % halo rows); one full wave of ~40-row blocks does the same work in fewer row-times.  Large grids
+// (many waves either way) get long chunks.
+// OFF by default - measured on B200 (profiles/r02k_phases.txt): the model is wrong where it matters.  4096x1024: predictor
+// 44.4 -> 46.8 us, K2+K3 54.4 -> 57.5, finalize 77 -> 94 us (one wave of long blocks hides latency worse than 2.6 waves of
+// short ones: every block starts with a dependent prologue of loads, and block turnover is what overlaps them); 16384^2:
+// finalize 3.09 -> 2.99 ms, the other two 1 % slower.  B200CFD_RPB_MODEL=1 turns it on.
+static inline int pick_rpb(int bx, int ny, int slots, int halo_rows, int fallback) {
+    static const int on = getenv("B200CFD_RPB_MODEL") ? atoi(getenv("B200CFD_RPB_MODEL")) : 0;
+    if (!on || (long long)bx * ((ny + 7) / 8) < 2ll * slots) return fallback;       // tiny grids: keep the latency rule
+    int best = fallback;
+    double best_cost = 1e300;
+    for (int rpb = 8; rpb <= 128; ++rpb) {
+        const long long nblk = (long long)bx * ((ny + rpb - 1) / rpb);
+        const long long waves = (nblk + slots - 1) / slots;
+        const double cost = (double)waves * (rpb + halo_rows + 6);
+        if (cost < best_cost) { best_cost = cost; best = rpb; }
+    }
+    return best;
+}
+
 static inline int rows_per_block(const Geom& g, int n_sm) {
     // enough blocks for ~8 blocks per SM, chunks of 8..64 rows (multiples of the flag tile height)
     const int bx = (g.nx + FCOLS - 1) / FCOLS;
@@ -183,7 +206,7 @@ static inline int rows_per_block(const Geom& g, int n_sm) {
     while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
-    return rpb;
+    return pick_rpb(bx, g.ny, 5 * n_sm, 2, rpb);             // k_predictor_fast: 5 blocks per SM (launch bounds)
 }
 
 bool fast_path_ok(const Geom& g, const void* const* ptrs, int n) {
@@ -363,6 +386,8 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
         const bool ownx = owner && c0 >= g.own0 && c0 < g.own1, owny = owner && c0 + 1 >= g.own0 && c0 + 1 < g.own1;
         const double i2dx = 1.0 / Rnd<T>::r(g.two_dx), i2dy = 1.0 / Rnd<T>::r(g.two_dy);
         const double vmax = p.max_velocity, fs = ctl->fs, pert = ctl->pert_scale, phase = ctl->phase;
+        // reduction weights: interior cells of the owned columns (divergence, vorticity) / owned columns (energy, maxima)
+        const double wdx = (inx && ownx) ? 1.0 : 0.0, wdy = (iny && owny) ? 1.0 : 0.0, wox = ownx ? 1.0 : 0.0, woy = owny ? 1.0 : 0.0;
         const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
         // wall rows: u = v = 0 (v5.py:357-360); they count in the energy mean
         if (owner && r0 == 0) { st2<T>(u, c0, 0.0, 0.0); st2<T>(v, c0, 0.0, 0.0); acc.cnt += (ownx ? 1 : 0) + (owny ? 1 : 0); }
@@ -472,35 +497,32 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
                 D2 gun = {0, 0};
                 if (i + 1 < g.ny - 1) { gun.x = Rnd<T>::r(fun.x * mn.x); gun.y = Rnd<T>::r(fun.y * mn.y); }
                 const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), gvW = shfl_up1(gvc.y), gvE = shfl_dn1(gvc.x);
+                // Branch-free from here on (the ncu source page of the branchy form: 15 % of the issue slots on BSSY / BSYNC /
+                // BRA, 6 % on ISETP): every lane does the arithmetic, ownership enters the reductions as 0 / 1 weights (a NaN or
+                // Inf times 0 is NaN, which fmax drops exactly like the nanmax it replaces), only the stores are predicated.
+                uchar2 mk = make_uchar2(0, 0);
+                if (has_mask && owner) mk = *reinterpret_cast<const uchar2*>(mask + ro + c0);
+                const double Dx = Rnd<T>::r((fuc.y - fuW) * g.hdx + (fvn.x - fvm.x) * g.hdy);
+                const double Dy = Rnd<T>::r((fuE - fuc.x) * g.hdx + (fvn.y - fvm.y) * g.hdy);
+                acc.dmax = fmax(acc.dmax, fmax(fabs(Dx) * wdx, fabs(Dy) * wdy));
+                const double Wx = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvc.y - gvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.x - gum.x) * i2dy));
+                const double Wy = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvE - gvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.y - gum.y) * i2dy));
+                acc.wmax = fmax(acc.wmax, fmax(fabs(Wx) * (mk.x ? 0.0 : wdx), fabs(Wy) * (mk.y ? 0.0 : wdy)));
+                const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.x * guc.x) + Rnd<T>::r(gvc.x * gvc.x)));
+                const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.y * guc.y) + Rnd<T>::r(gvc.y * gvc.y)));
+                const double cux = fmin(fmax(guc.x, -vmax), vmax), cuy = fmin(fmax(guc.y, -vmax), vmax);
+                const double cvx = fmin(fmax(gvc.x, -vmax), vmax), cvy = fmin(fmax(gvc.y, -vmax), vmax);
                 if (owner) {
-                    uchar2 mk = make_uchar2(0, 0);
-                    if (has_mask) mk = *reinterpret_cast<const uchar2*>(mask + ro + c0);
-                    if (inx && ownx) {
-                        acc.dmax = fmax(acc.dmax, fabs(Rnd<T>::r((fuc.y - fuW) * g.hdx + (fvn.x - fvm.x) * g.hdy)));
-                        if (!mk.x) acc.wmax = fmax(acc.wmax, fabs(Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvc.y - gvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.x - gum.x) * i2dy))));
-                    }
-                    if (iny && owny) {
-                        acc.dmax = fmax(acc.dmax, fabs(Rnd<T>::r((fuE - fuc.x) * g.hdx + (fvn.y - fvm.y) * g.hdy)));
-                        if (!mk.y) acc.wmax = fmax(acc.wmax, fabs(Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(gvE - gvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(gun.y - gum.y) * i2dy))));
-                    }
-                    const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.x * guc.x) + Rnd<T>::r(gvc.x * gvc.x)));
-                    const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(guc.y * guc.y) + Rnd<T>::r(gvc.y * gvc.y)));
-                    const double cux = fmin(fmax(guc.x, -vmax), vmax), cuy = fmin(fmax(guc.y, -vmax), vmax);
-                    const double cvx = fmin(fmax(gvc.x, -vmax), vmax), cvy = fmin(fmax(gvc.y, -vmax), vmax);
                     // np.clip propagates NaN; fmin/fmax would drop it
                     st2<T>(u, ro + c0, guc.x == guc.x ? cux : guc.x, guc.y == guc.y ? cuy : guc.y);
                     st2<T>(v, ro + c0, gvc.x == gvc.x ? cvx : gvc.x, gvc.y == gvc.y ? cvy : gvc.y);
-                    if (ownx) {
-                        if (ex == ex) { acc.e += ex; acc.cnt += 1; }
-                        if (!isfinite(guc.x) || !isfinite(gvc.x)) acc.bad = 1;
-                        acc.mu = fmax(acc.mu, fabs(cux)); acc.mv = fmax(acc.mv, fabs(cvx));
-                    }
-                    if (owny) {
-                        if (ey == ey) { acc.e += ey; acc.cnt += 1; }
-                        if (!isfinite(guc.y) || !isfinite(gvc.y)) acc.bad = 1;
-                        acc.mu = fmax(acc.mu, fabs(cuy)); acc.mv = fmax(acc.mv, fabs(cvy));
-                    }
                 }
+                const bool okx = ownx && ex == ex, oky = owny && ey == ey;           // nanmean: NaN cells are not counted
+                acc.e += okx ? ex : 0.0; acc.cnt += okx ? 1u : 0u;
+                acc.e += oky ? ey : 0.0; acc.cnt += oky ? 1u : 0u;
+                acc.bad |= (ownx && (!isfinite(guc.x) || !isfinite(gvc.x))) || (owny && (!isfinite(guc.y) || !isfinite(gvc.y))) ? 1u : 0u;
+                acc.mu = fmax(acc.mu, fmax(fabs(cux) * wox, fabs(cuy) * woy));
+                acc.mv = fmax(acc.mv, fmax(fabs(cvx) * wox, fabs(cvy) * woy));
                 gum = guc; fvm = fvc; fuc = fun; fvc = fvn; mc = mn; mn = mn2;
                 pm = pc; pc = pn; pn = pn2; urn = urn2; vrn = vrn2;
             }
@@ -527,6 +549,7 @@ static inline dim3 finalize_fast_grid(const Geom& g, int n_sm, int* rpb_out) {
     while (rpb > rpb_min && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
+    rpb = pick_rpb(bx, g.ny, 3 * n_sm, 3, rpb);              // k_finalize_fast: 3 blocks per SM
     *rpb_out = rpb;
     return dim3(bx, (g.ny + rpb - 1) / rpb);
 }
@@ -711,6 +734,7 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
     while (rpb > 16 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
+    rpb = pick_rpb(bx, g.ny, 4 * n_sm, 4, rpb);              // k_div_rb1_correct_fast: 4 blocks per SM
     const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
 #define DCF(T, DIV) launch_pdl(k_div_rb1_correct_fast<T, DIV>, grid, dim3(FBT), s, g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)

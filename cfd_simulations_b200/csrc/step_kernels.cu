@@ -241,7 +241,7 @@ __device__ void ctl_prepare(StepCtl* c, const CtlParams& cp) {
     const long long step = c->step;
     double dt;
     if (!cp.adaptive_dt) dt = cp.dt_base;
-    else if (step < 1000) dt = (double)(float)0.00002;
+    else if (step < 1000) dt = cp.scalar_f32 ? (double)(float)0.00002 : 0.00002;
     else {
         double vm = fmax(fmax(c->in_max_u, c->in_max_v), 1e-10);
         const double dt_cfl = cp.cfl_target * cp.hmin / vm;
@@ -257,12 +257,12 @@ __device__ void ctl_prepare(StepCtl* c, const CtlParams& cp) {
         } else {
             dt = fmin(dt_cfl, dt_visc);
             dt = fmin(fmax(dt, cp.dt_min), cp.dt_max);
-            dt = (double)(float)dt;
+            if (cp.scalar_f32) dt = (double)(float)dt;           // v5: np.float32(...); v3 / v4: float(...)
         }
     }
     c->dt = dt;
     c->fs = fmin(1.0, (double)step / (double)cp.initial_steps);
-    c->pert_scale = fmin(1.0, (double)step / 1000.0) * 0.01;
+    c->pert_scale = fmin(1.0, (double)step / 1000.0) * cp.pert_amplitude;
     c->phase = 0.02 * (double)step;
     c->max_div_pre = c->max_grad = c->max_div_post = c->max_vort = c->max_u = c->max_v = 0ull;
     c->nonfinite = 0u;
@@ -425,9 +425,9 @@ void launch_field_sum(int dtype, const Geom& g, const void* f, double* partials,
              (k_field_sum<float><<<NUT_PARTS, 256, 0, s>>>(g, (const float*)f, partials)));
 }
 void launch_apply_bc(int dtype, const Geom& g, void* u, void* v, const double* y, double V_inf, double y_max,
-                     long long step, cudaStream_t s) {
+                     long long step, cudaStream_t s, double amplitude) {
     const double sc = (double)step / 1000.0;
-    const double pert_scale = (sc < 1.0 ? sc : 1.0) * 0.01, phase = 0.02 * (double)step;
+    const double pert_scale = (sc < 1.0 ? sc : 1.0) * amplitude, phase = 0.02 * (double)step;
     const int n = g.ny + g.nx;
     DISPATCH(dtype,
              (k_apply_bc<double><<<(n + 255) / 256, 256, 0, s>>>(g, (double*)u, (double*)v, y, V_inf, y_max, pert_scale, phase)),

@@ -38,9 +38,9 @@ def _health_ok(solver, step) -> bool:
     u, v = solver.u, solver.v                                   # v5.py:599-613 on host arrays
     if not (np.all(np.isfinite(u)) and np.all(np.isfinite(v))):
         return False
-    if max(np.max(np.abs(u)), np.max(np.abs(v))) > 5.0:
-        return False
     cfg = solver.config
+    if max(np.max(np.abs(u)), np.max(np.abs(v))) > cfg.max_velocity:         # v5.py:604
+        return False
     div = np.zeros_like(u)
     div[1:-1, 1:-1] = (u[1:-1, 2:] - u[1:-1, :-2]) / (2 * cfg.dx) + (v[2:, 1:-1] - v[:-2, 1:-1]) / (2 * cfg.dy)
     return float(np.max(np.abs(div))) <= (20.0 if step <= 1000 else 2.0)
@@ -71,7 +71,10 @@ def run_simulation(solver, writer=None, T_total=None, max_steps=None, health_int
         if chunked:
             to_health = (-step) % health_interval + 1
             to_save = (-step) % save_interval + 1 if writer is not None else 1 << 30
-            certain = int((T_total - res.current_time) / dt_max)          # steps that cannot overshoot T_total
+            # steps that cannot overshoot T_total.  The clock accumulates in float32 (see below): near t ~ 30 one add can
+            # round up by ulp32(t) ~ 2e-6 against dt ~ 1e-4, so the bound counts that rounding in and keeps one step in hand
+            ulp32 = float(np.spacing(np.float32(max(T_total, 1e-30)))) if acc32 else 0.0
+            certain = int((T_total - res.current_time) / (dt_max + ulp32)) - 1
             n = max(1, min(to_health, to_save, certain, 4096))
             if max_steps is not None:
                 n = max(1, min(n, max_steps - step))

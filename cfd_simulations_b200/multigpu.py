@@ -193,6 +193,18 @@ class LocalSlabs:
 
     def refresh_halos(self, names=("u", "v")):
         S = self.slabs
+        if tuple(names) == ("u", "v") and all(s._halo is not None and s._halo.halo_rows is not None for s in S):
+            # the product's path: all fields and both sides in one launch per slab (b200cfd_halo_rows), the "message" being
+            # the neighbour's send buffer
+            for s in S:
+                p, hx = s.plan, s._halo
+                hx.halo_rows(True, [s._d[n] for n in names], p.own0, p.send_left, hx.sbuf_l, p.own1 - p.send_right, p.send_right, hx.sbuf_r)
+            for i, s in enumerate(S):
+                p, hx = s.plan, s._halo
+                left = S[i - 1]._halo.sbuf_r if i > 0 else None
+                right = S[i + 1]._halo.sbuf_l if i + 1 < len(S) else None
+                hx.halo_rows(False, [s._d[n] for n in names], 0, p.halo_left, left, p.own1, p.halo_right, right)
+            return
         for a, b in zip(S[:-1], S[1:]):          # a is the left neighbour of b
             pa, pb = a.plan, b.plan
             for k, name in enumerate(names):

@@ -41,7 +41,9 @@ def make_c_config(cfg, ny, nx, poisson_mode, cleandiv_mode, omega, clean_iters, 
         dt_base=float(cfg.dt_base), max_velocity=float(cfg.max_velocity), cs=float(cfg.smagorinsky_constant),
         pressure_tolerance=float(cfg.pressure_tolerance), omega=float(omega),
         rank=rank, nranks=nranks, nx_global=nx if nx_global is None else nx_global, x_offset=x_offset,
-        halo_left=halo_left, halo_right=halo_right)
+        halo_left=halo_left, halo_right=halo_right,
+        pert_amplitude=float(getattr(cfg, "perturbation_amplitude", 0.01)),
+        scalar_f32=int(getattr(cfg, "float32_scalars", True)), variant_set=1)
 
 
 class OptimizedTurbulentSolver:
@@ -273,7 +275,7 @@ class OptimizedTurbulentSolver:
         self.advance(1)
         self._sync_scalars()
         dt = self.scalars[-1]["dt"]
-        return np.float32(dt) if self.config.adaptive_dt else dt
+        return np.float32(dt) if (self.config.adaptive_dt and getattr(self.config, "float32_scalars", True)) else dt
 
     def time_step_host(self, u_host, v_host, n_steps=1):
         """time_step() on HOST arrays, the way the reference owns its state: uploads u, v, runs n_steps,
@@ -298,7 +300,9 @@ class OptimizedTurbulentSolver:
             self.scalars.append(rec)
             st = int(rec["step"])
             self._energy_history.append((st, rec["mean_energy"]))     # v5.py:433
-            self._times.append(st * rec["dt"])                        # v5.py:434
+            # v5.py:434 `self.step * dt`: with dt an np.float32 (v5) the product is a float32 (NumPy 2 promotion)
+            self._times.append(float(np.float32(st) * np.float32(rec["dt"])) if getattr(self.config, "float32_scalars", True)
+                               and self.config.adaptive_dt else st * rec["dt"])
         self._fetched = self._step
 
     def adaptive_time_step(self):

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200CFD_ABI_VERSION 2
+#define B200CFD_ABI_VERSION 3
 
 enum { B200CFD_F64 = 0, B200CFD_F32 = 1 };
 enum { B200CFD_OK = 0, B200CFD_EINVAL = -1, B200CFD_ECUDA = -2, B200CFD_ENOMEM = -3, B200CFD_ESTATE = -4 };
@@ -62,6 +62,11 @@ typedef struct b200cfd_config {
      * x_offset = global column of local column 0; local columns [halo_left, nx - halo_right) are owned,
      * the others are halo columns (recomputed redundantly, refreshed by the caller once per step). */
     int32_t rank, nranks, nx_global, x_offset, halo_left, halo_right;
+    /* v3 / v4 variants of the same step, honoured when variant_set != 0 (else the v5 values 0.01 / 1):
+     * pert_amplitude = inflow perturbation amplitude (v5.py:351, v4.py:349: 0.01; v3.py:329: 0.005);
+     * scalar_f32 = the warm-up dt and the adaptive dt are float32-rounded (v5.py:321,326) or plain doubles (v4.py:319,324). */
+    double  pert_amplitude;
+    int32_t scalar_f32, variant_set;
 } b200cfd_config;
 
 /* Per-step diagnostics, the five values v5.py logs each step (:410,:415,:422,:429,:435) plus dt. */

@@ -36,6 +36,11 @@ typedef struct {
     int poisson_mode, pressure_iterations;
     double pressure_tolerance, omega;
     int clean_iters;
+    /* v3 / v4 variants of the same step: inflow perturbation amplitude (v5, v4: 0.01, v4.py:349; v3: 0.005, v3.py:329) and
+     * whether the scalars nu, dt, artificial_viscosity and the adaptive dt are float32-rounded (v5.py:80-82,321,326) or
+     * plain Python floats (v3 / v4: v4.py:79-80,319,324) */
+    double pert_amplitude;
+    int scalar_f32;
 } orc_config;
 
 #define CAT_(a, b) a##b

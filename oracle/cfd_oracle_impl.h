@@ -141,10 +141,15 @@ void SFX(orc_smagorinsky)(const T* u, const T* v, T* nu_t, int ny, int nx, doubl
 }
 
 /* v5.py:349-360 apply_boundary_conditions — order matters: inflow col, outflow col, then walls */
+void SFX(orc_apply_bc_amp)(T* u, T* v, int ny, int nx, const double* y, double y_max, double V_inf, long step, double amplitude);
 void SFX(orc_apply_bc)(T* u, T* v, int ny, int nx, const double* y, double y_max, double V_inf, long step)
 {
+    SFX(orc_apply_bc_amp)(u, v, ny, nx, y, y_max, V_inf, step, 0.01);
+}
+void SFX(orc_apply_bc_amp)(T* u, T* v, int ny, int nx, const double* y, double y_max, double V_inf, long step, double amplitude)
+{
     double sc = (double)step / 1000.0;
-    const double pert_scale = (sc < 1.0 ? sc : 1.0) * 0.01;
+    const double pert_scale = (sc < 1.0 ? sc : 1.0) * amplitude;
     for (int i = 0; i < ny; ++i) {
         double pert = pert_scale * sin(2 * M_PI * y[i] / y_max + 0.02 * (double)step);
         u[IDX(i, 0)] = (T)(V_inf * (1 + pert));
@@ -308,7 +313,7 @@ double SFX(orc_max_abs)(const T* a, size_t n)
 double SFX(orc_adaptive_dt)(const orc_config* c, const T* u, const T* v, const T* nu_t, long step)
 {
     if (!c->adaptive_dt) return c->dt_base;
-    if (step < 1000) return (double)(float)0.00002;
+    if (step < 1000) return c->scalar_f32 ? (double)(float)0.00002 : 0.00002;
     size_t n = (size_t)c->ny * c->nx;
     double vm = SFX(orc_max_abs)(u, n), vm2 = SFX(orc_max_abs)(v, n);
     if (vm2 > vm) vm = vm2;
@@ -333,7 +338,7 @@ double SFX(orc_adaptive_dt)(const orc_config* c, const T* u, const T* v, const T
     double dt = dt_cfl < dt_visc ? dt_cfl : dt_visc;
     if (dt < c->dt_min) dt = c->dt_min;
     if (dt > c->dt_max) dt = c->dt_max;
-    return (double)(float)dt;
+    return c->scalar_f32 ? (double)(float)dt : dt;      /* v5: np.float32(...); v3 / v4: float(...) */
 }
 
 /* v5.py:375-441 OptimizedTurbulentSolver.time_step(), in execution order.
@@ -376,7 +381,7 @@ double SFX(orc_time_step)(const orc_config* c, T* u, T* v, T* phi, T* u_star, T*
             v_star[k] = (T)((float)v[k] + fdt * (-(float)conv_v[k] + (float)lap_v[k]));
         }
     }
-    SFX(orc_apply_bc)(u_star, v_star, ny, nx, y, c->y_max, c->V_inf, step);
+    SFX(orc_apply_bc_amp)(u_star, v_star, ny, nx, y, c->y_max, c->V_inf, step, c->pert_amplitude);
     double fs = (double)step / (double)c->initial_steps; if (fs > 1.0) fs = 1.0;
     SFX(orc_apply_ibm)(u_star, v_star, ibm, ny, nx, fs);
     SFX(orc_divergence)(u_star, v_star, div, ny, nx, c->dx, c->dy);
@@ -414,7 +419,7 @@ double SFX(orc_time_step)(const orc_config* c, T* u, T* v, T* phi, T* u_star, T*
     SFX(orc_clean_divergence)(u, v, ny, nx, c->dx, c->dy, c->clean_iters, work, NULL);
     SFX(orc_divergence)(u, v, work, ny, nx, c->dx, c->dy);
     scal[3] = SFX(orc_max_abs)(work, n);
-    SFX(orc_apply_bc)(u, v, ny, nx, y, c->y_max, c->V_inf, step);
+    SFX(orc_apply_bc_amp)(u, v, ny, nx, y, c->y_max, c->V_inf, step, c->pert_amplitude);
     SFX(orc_apply_ibm)(u, v, ibm, ny, nx, fs);
     scal[4] = SFX(orc_max_vorticity)(u, v, mask, ny, nx, c->dx, c->dy);
     scal[5] = SFX(orc_mean_energy)(u, v, ny, nx);

@@ -63,6 +63,7 @@ class OrcConfig(C.Structure):
         ("poisson_mode", C.c_int), ("pressure_iterations", C.c_int),
         ("pressure_tolerance", C.c_double), ("omega", C.c_double),
         ("clean_iters", C.c_int),
+        ("pert_amplitude", C.c_double), ("scalar_f32", C.c_int),
     ]
 
 

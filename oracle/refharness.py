@@ -49,6 +49,7 @@ def load(path: Path, modname: str):
     scratch = tempfile.mkdtemp(prefix="refcwd_")
     cwd = os.getcwd()
     os.chdir(scratch)
+    os.makedirs("logs", exist_ok=True)          # v3 / v4 open logs/<name>.log at import without creating the directory
     try:
         spec = importlib.util.spec_from_file_location(modname, str(path))
         mod = importlib.util.module_from_spec(spec)

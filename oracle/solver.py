@@ -37,7 +37,9 @@ class OracleTurbulentSolver:
             initial_steps=cfg.initial_steps, use_supg=int(cfg.use_supg), use_les=int(cfg.use_les),
             adaptive_dt=int(cfg.adaptive_dt), cs=cfg.smagorinsky_constant, poisson_mode=self.poisson_mode,
             pressure_iterations=cfg.pressure_iterations, pressure_tolerance=cfg.pressure_tolerance,
-            omega=omega, clean_iters=clean_iters)
+            omega=omega, clean_iters=clean_iters,
+            pert_amplitude=float(getattr(cfg, "perturbation_amplitude", 0.01)),
+            scalar_f32=int(getattr(cfg, "float32_scalars", True)))
         self._mask_u8 = np.ascontiguousarray(self.cylinder_mask, dtype=np.uint8)
         self._work = np.empty((8, cfg.ny, cfg.nx), dtype=dt)
         self._fn = getattr(orc.lib(), "orc_time_step" + ("_f32" if dt == np.float32 else "_f64"))
@@ -53,4 +55,4 @@ class OracleTurbulentSolver:
         self.energy_history.append((self.step, s[5]))
         self.times.append(self.step * dt)
         self.step += 1
-        return np.float32(dt) if self.config.adaptive_dt else dt
+        return np.float32(dt) if (self.config.adaptive_dt and getattr(self.config, "float32_scalars", True)) else dt

@@ -21,7 +21,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in sorted(declared) if not hasattr(lib, s)]
     assert not missing, missing
     assert set(_lib.EXPORTS) <= declared
-    assert lib.b200cfd_abi_version() == 2
+    assert lib.b200cfd_abi_version() == 3
 
 
 def test_config_struct_layout_matches_header():

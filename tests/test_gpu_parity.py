@@ -473,3 +473,77 @@ def test_c2_10k_steps_drag_lift_series_vs_oracle():
         a, b = getattr(s, name)[::st, ::st], g["final_" + name]
         assert rel_l2(a, b) <= 1e-9, name
     s.close()
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_guard_bands_around_every_bound_field(f32):
+    """Stand-in for compute-sanitizer memcheck (closed on this pool, profiles/r02i_sanitizer.md): every caller-owned field
+    is a view into a larger allocation whose guard bands hold a NaN sentinel.  After 6 steps the bands must be bit-identical
+    (no out-of-bounds write) and u, v, phi bit-identical to a run on plain allocations (an out-of-bounds read that reaches a
+    result would poison it with NaN).  1024x256 takes the TMA sweeps, the fused corrections and the fast kernels."""
+    import ctypes as C
+    import torch
+    from cfd_simulations_b200._lib import check
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=1024, ny=256, memory_efficient=f32)
+    ref = OptimizedTurbulentSolver(cfg)
+    s = OptimizedTurbulentSolver(cfg)
+    G = 4096
+    names = ("u", "v", "phi", "u_star", "v_star", "div_u_star", "tau_supg", "nu_t")
+    big, view = {}, {}
+    for n in names:
+        t = s._d[n]
+        b = torch.full((t.numel() + 2 * G,), float("nan"), dtype=t.dtype, device=t.device)
+        v = b[G:G + t.numel()].view(t.shape)
+        v.copy_(t)
+        big[n], view[n] = b, v
+    d = s._d
+    check(s._lib.b200cfd_bind_fields(s._h, view["u"].data_ptr(), view["v"].data_ptr(), view["phi"].data_ptr(),
+                                     view["u_star"].data_ptr(), view["v_star"].data_ptr(), view["div_u_star"].data_ptr(),
+                                     view["tau_supg"].data_ptr(), view["nu_t"].data_ptr(), d["ibm"].data_ptr(),
+                                     d["mask"].data_ptr(), d["y"].data_ptr()), s._h)
+    for n in names:
+        d[n] = view[n]
+    s.step = 0
+    ref.advance(6)
+    s.advance(6)
+    torch.cuda.synchronize()
+    for n in names:
+        b = big[n]
+        assert bool(torch.isnan(b[:G]).all()) and bool(torch.isnan(b[-G:]).all()), n
+    for n in ("u", "v", "phi", "u_star", "v_star", "div_u_star"):
+        assert torch.equal(view[n], ref._d[n]), n
+    assert bool(torch.isfinite(view["u"]).all())
+    s.close(); ref.close()
+
+
+def _gpu_variant(name, f32, check_dt, solver_kw, **cfg_kw):
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    g, meta = load(name)
+    s = OptimizedTurbulentSolver(OptimizedTurbulentConfig(nx=150, ny=46, memory_efficient=f32, **cfg_kw), **solver_kw)
+    s.step = int(g["start_step"])
+    s.advance(25)
+    s._sync_scalars()
+    if check_dt:
+        assert [r["dt"] for r in s.scalars[-25:]] == [float(x) for x in g["dts"]]
+    tol = TOL["f32" if f32 else "f64"]
+    assert rel_l2(s.u, g["u_25"]) <= tol and rel_l2(s.v, g["v_25"]) <= tol * (1 if not f32 else 3)
+    assert rel_l2(s.phi, g["phi_25"]) <= tol * (1 if not f32 else 10) and rel_l2(s.u_star, g["ustar_25"]) <= tol
+    s.close()
+    return meta
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_v4_variant_vs_reference_golden(f32):
+    """v4.py (Python-float nu / dt, unrounded adaptive dt: v4.py:79-80,319,324) through float32_scalars=False."""
+    m = _gpu_variant(f"steps_46x150_v4_from990_{'f32' if f32 else 'f64'}.npz", f32, True, {}, float32_scalars=False)
+    assert m["reference"].endswith("v4.py")
+
+
+def test_v3_variant_vs_reference_golden():
+    """v3.py: inflow perturbation 0.005 (v3.py:329), Python-float scalars, its own default Re = 200 (v3.py:41)."""
+    m = _gpu_variant("steps_46x150_v3_from990_f64.npz", False, False, {}, float32_scalars=False,
+                     perturbation_amplitude=0.005, Re=200.0)
+    assert m["reference"].endswith("v3.py")

@@ -137,3 +137,32 @@ def test_step_ladder_3000_fp64():
                 assert rel_l2(getattr(s, name)[::k, ::k], g[f"{name}_{n}"]) <= 1e-12, (name, n)
     e = np.array([x for _, x in s.energy_history])
     assert np.allclose(e, g["energy"], rtol=1e-12)
+
+
+def _variant(name, f32, check_dt, solver_kw, **cfg_kw):
+    g, meta = load(name)
+    cfg = OptimizedTurbulentConfig(nx=150, ny=46, memory_efficient=f32, **cfg_kw)
+    s = OracleTurbulentSolver(cfg, **solver_kw)
+    s.step = int(g["start_step"])
+    tol = TOL["f32" if f32 else "f64"]
+    for k in range(25):
+        dt = s.time_step()
+        if check_dt:
+            assert float(dt) == float(g["dts"][k]), k
+    assert rel_l2(s.u, g["u_25"]) <= tol and rel_l2(s.v, g["v_25"]) <= tol * (1 if not f32 else 3)
+    assert rel_l2(s.phi, g["phi_25"]) <= tol * (1 if not f32 else 10) and rel_l2(s.u_star, g["ustar_25"]) <= tol
+    return meta
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_v4_variant_unrounded_scalars(f32):
+    """v4.py = v5.py with Python-float nu / dt and an unrounded adaptive dt (v4.py:79-80,319,324): float32_scalars=False."""
+    m = _variant(f"steps_46x150_v4_from990_{'f32' if f32 else 'f64'}.npz", f32, True, {}, float32_scalars=False)
+    assert m["reference"].endswith("v4.py")
+
+
+def test_v3_variant_half_perturbation():
+    """v3.py: inflow perturbation 0.005 (v3.py:329), Python-float scalars, its own default Re = 200 (v3.py:41)."""
+    m = _variant("steps_46x150_v3_from990_f64.npz", False, False, {}, float32_scalars=False,
+                 perturbation_amplitude=0.005, Re=200.0)
+    assert m["reference"].endswith("v3.py")

@@ -71,7 +71,7 @@ EULER_EXPORTS = [
 EXPORTS = [
     "b200cfd_abi_version", "b200cfd_last_error", "b200cfd_device_count", "b200cfd_create", "b200cfd_destroy",
     "b200cfd_bind_fields", "b200cfd_set_step", "b200cfd_get_step", "b200cfd_step", "b200cfd_step_host",
-    "b200cfd_launches_per_step", "b200cfd_health", "b200cfd_profile_begin", "b200cfd_profile_end", "b200cfd_get_clean_plan", "b200cfd_fetch_scalars", "b200cfd_poisson", "b200cfd_poisson_info",
+    "b200cfd_launches_per_step", "b200cfd_health", "b200cfd_profile_begin", "b200cfd_profile_end", "b200cfd_get_clean_plan", "b200cfd_fetch_scalars", "b200cfd_poisson", "b200cfd_poisson_info", "b200cfd_poisson_keep_rhs",
     "b200cfd_k_supg_tau", "b200cfd_k_convection", "b200cfd_k_laplacian", "b200cfd_k_divergence",
     "b200cfd_k_gradient", "b200cfd_k_smagorinsky", "b200cfd_k_vorticity", "b200cfd_k_apply_bc", "b200cfd_k_apply_ibm",
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
@@ -112,6 +112,7 @@ def load():
     lib.b200cfd_poisson.argtypes = [vp, vp, vp, vp, dbl, dbl, dbl, i32, i32, dbl, dbl, i32, C.POINTER(i32),
                                     C.POINTER(dbl), vp]
     lib.b200cfd_poisson_info.argtypes = [vp, C.POINTER(C.c_int * 4)]
+    lib.b200cfd_poisson_keep_rhs.argtypes = [vp, i32]
     lib.b200cfd_k_supg_tau.argtypes = [vp, vp, vp, vp, dbl, dbl, vp]
     lib.b200cfd_k_convection.argtypes = [vp, vp, vp, vp, vp, vp, i32, vp]
     lib.b200cfd_k_laplacian.argtypes = [vp, vp, vp, dbl, vp]

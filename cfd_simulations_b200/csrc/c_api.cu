@@ -793,6 +793,15 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
     return B200CFD_OK;
 }
 
+// keep != 0: the following b200cfd_poisson calls solve on the SAME, unchanged rhs_div and mask arrays as the previous call
+// (one solve done in chunks around halo refreshes): the temporally blocked kernel's classified copy of the right-hand side is
+// not rebuilt per call.  Reset with keep = 0 before the right-hand side changes.
+int b200cfd_poisson_keep_rhs(b200cfd_handle* h, int keep) {
+    if (!h) return B200CFD_EINVAL;
+    poisson_tb_keep_rhs(&h->tb, keep);
+    return B200CFD_OK;
+}
+
 // What the last b200cfd_poisson call did: out4 = {temporal depth used (1 = one-sweep kernels), HBM passes of the
 // temporally blocked kernel (0 when it did not run), bytes per cell per pass of that kernel, reserved}.
 int b200cfd_poisson_info(b200cfd_handle* h, int* out4) {

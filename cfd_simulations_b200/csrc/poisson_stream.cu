@@ -187,10 +187,13 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         }
         // column flags as multiplicative masks: owned by this tile AND by this slab (max|dphi| only)
         double ownm[SPL];
+        bool own_lane = true, own_any = false;
 #pragma unroll
         for (int m = 0; m < SPL; ++m) {
             const int c = c0 + m;
             ownm[m] = (c >= x0 && c < x0 + P.OW && c >= P.own0 && c < P.own1 && c < P.nx) ? 1.0 : 0.0;
+            own_lane = own_lane && ownm[m] != 0.0;
+            own_any = own_any || ownm[m] != 0.0;
         }
         // colour of this lane's columns: c0 is a multiple of 4, so cells 0, 2 have the parity of (row + jg0), cells 1, 3 the other
         const int colpar = P.jg0 & 1;
@@ -255,7 +258,13 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                         pn = Rnd<T>::r(pn);
                         if (SPECIAL) pn = sel_int(act, sel_lt(fabs(r[m]), INF, pn, C[m]), C[m]);   // masked / border / inactive: kept
                         out[m] = pn;
-                        if (CHECK) ch[k / 2] = fmax(ch[k / 2], sel_int(rown, fabs(pn - C[m]) * ownm[m], 0.0));
+                        // ownership is per lane (window origin, owned width, slab bounds and nx are all multiples of 4) and the
+                        // row test is warp-uniform: one predicate guards a 3-instruction update instead of a multiply and two selects
+                        // (a lane cut by an unaligned slab boundary keeps the per-cell weight)
+                        if (CHECK && rown) {
+                            if (own_lane) ch[k / 2] = fmax(ch[k / 2], fabs(pn - C[m]));
+                            else if (own_any) ch[k / 2] = fmax(ch[k / 2], fabs(pn - C[m]) * ownm[m]);
+                        }
                     };
                     if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
                     else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }
@@ -381,6 +390,11 @@ struct PoissonStream {
     StreamCtl* ctl = nullptr;
     uint8_t* tflags = nullptr;             // one byte per tile: its window contains masked / never-updated cells
     size_t tflags_cap = 0;
+    // what rhs_s / tflags were built from: a caller that solves in chunks on an UNCHANGED right-hand side (the slab solver:
+    // a few iterations, halo refresh, a few more) declares it with poisson_stream_keep_rhs and skips the rebuild
+    const void* rhs_src = nullptr; const void* mask_src = nullptr;
+    int rhs_ny = 0, rhs_nx = 0, rhs_L = 0, rhs_tile_h = 0, rhs_dtype = -1;
+    bool keep_rhs = false;
     int last_depth = 0, last_passes = 0;
 };
 static std::string g_stream_err;
@@ -389,6 +403,10 @@ void poisson_stream_destroy(PoissonStream* ps) {
     if (!ps) return;
     cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->tflags);
     delete ps;
+}
+void poisson_stream_keep_rhs(PoissonStream** pps, int keep) {
+    if (!*pps) *pps = new PoissonStream();
+    (*pps)->keep_rhs = keep != 0;
 }
 void poisson_stream_info(const PoissonStream* ps, int* depth, int* passes) {
     *depth = ps ? ps->last_depth : 0;
@@ -456,17 +474,16 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     const int es = dtype == 0 ? 8 : 4;
     if (iters <= 0) return 0;
     if (((uintptr_t)phi % 16) || ((g.pitch * es) % 16) || g.nx < 64 || g.ny < 16 || g.nx % 4) return 0;
-    if (!*pps) {
-        PoissonStream* ps = new PoissonStream();
-        if (cudaMalloc(&ps->slots, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&ps->ctl, sizeof(StreamCtl)) != cudaSuccess) {
-            cudaGetLastError(); g_stream_err = "cudaMalloc(control)"; delete ps; return -1;
-        }
-        *pps = ps;
-    }
+    if (!*pps) *pps = new PoissonStream();
     PoissonStream* ps = *pps;
+    if (!ps->slots) {
+        if (cudaMalloc(&ps->slots, 8 * sizeof(unsigned long long)) != cudaSuccess || cudaMalloc(&ps->ctl, sizeof(StreamCtl)) != cudaSuccess) {
+            cudaGetLastError(); g_stream_err = "cudaMalloc(control)"; return -1;
+        }
+    }
     const size_t bytes = (size_t)g.ny * g.pitch * es;
     if (ps->bytes < bytes) {
-        cudaFree(ps->rhs_s); cudaFree(ps->alt); ps->rhs_s = ps->alt = nullptr; ps->bytes = 0;
+        cudaFree(ps->rhs_s); cudaFree(ps->alt); ps->rhs_s = ps->alt = nullptr; ps->bytes = 0; ps->rhs_src = nullptr;
         if (cudaMalloc(&ps->rhs_s, bytes) != cudaSuccess || cudaMalloc(&ps->alt, bytes) != cudaSuccess) {
             cudaGetLastError(); g_stream_err = "cudaMalloc of the temporal-blocking scratch failed"; return -1;
         }
@@ -503,14 +520,18 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         if (cudaMalloc(&ps->tflags, ntile) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(tile flags)"; return -1; }
         ps->tflags_cap = ntile;
     }
-    if (cudaMemsetAsync(ps->tflags, 0, ntile, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile flags)"; return -1; }
+    const bool reuse = ps->keep_rhs && ps->rhs_src == div && ps->mask_src == (const void*)mask && ps->rhs_ny == g.ny &&
+                       ps->rhs_nx == g.nx && ps->rhs_L == L && ps->rhs_tile_h == P.tile_h && ps->rhs_dtype == dtype;
     const int VH = L + 3;                                           // rows above / below a chunk its pipeline touches
     const dim3 gnb((unsigned)((g.pitch + 255) / 256), (unsigned)(g.ny < 8192 ? g.ny : 8192));
     (void)nb;
-    if (dtype == 0) k_stream_make_rhs<double><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
+    if (reuse) { /* rhs_s and tflags still describe this right-hand side */ }
+    else if (cudaMemsetAsync(ps->tflags, 0, ntile, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile flags)"; return -1; }
+    else if (dtype == 0) k_stream_make_rhs<double><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
                                                                   ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
     else k_stream_make_rhs<float><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const float*)div, mask, (float*)ps->rhs_s,
                                                     ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
+    ps->rhs_src = div; ps->mask_src = mask; ps->rhs_ny = g.ny; ps->rhs_nx = g.nx; ps->rhs_L = L; ps->rhs_tile_h = P.tile_h; ps->rhs_dtype = dtype;
     CUtensorMap m_phi, m_alt, m_rhs, o_phi, o_alt;
     if (!tma_make_2d(&m_phi, dtype, phi, g.nx, g.ny, g.pitch, SW, SKR) || !tma_make_2d(&m_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, SW, SKR) ||
         !tma_make_2d(&m_rhs, dtype, ps->rhs_s, g.nx, g.ny, g.pitch, SW, SKR) ||

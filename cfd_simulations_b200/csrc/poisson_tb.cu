@@ -41,6 +41,10 @@ struct PoissonTB {
     bool last_stream = false;
 };
 
+void poisson_tb_keep_rhs(PoissonTB** ptb, int keep) {
+    if (!*ptb) *ptb = new PoissonTB();
+    poisson_stream_keep_rhs(&(*ptb)->stream, keep);
+}
 void poisson_tb_info(const PoissonTB* tb, int* depth, int* passes) {
     if (tb && tb->last_stream) { poisson_stream_info(tb->stream, depth, passes); return; }
     *depth = tb ? tb->last_depth : 0;

@@ -22,6 +22,10 @@ bool poisson_stream_enabled();                       // B200CFD_POISSON_STREAM=0
 const char* poisson_stream_error();
 void poisson_stream_destroy(PoissonStream* ps);
 void poisson_stream_info(const PoissonStream* ps, int* depth, int* passes);
+// keep != 0: the following solves use the SAME, unchanged right-hand side and mask arrays as the previous one (a solve done
+// in chunks around halo refreshes): the classified copy of the rhs and the tile flags are not rebuilt
+void poisson_stream_keep_rhs(PoissonStream** ps, int keep);
+void poisson_tb_keep_rhs(PoissonTB** tb, int keep);
 // mode 0: Jacobi (scale = dx^2/dt), mode 1: red-black (scale = -1/dt).  tol > 0 (mode 1): device-side stop at exactly the
 // iteration the sequential algorithm stops at; the host polls once per batch of passes.
 int poisson_stream_run(PoissonStream** ps, int dtype, int mode, const Geom& g, int n_sm, void* phi, const void* div,

@@ -174,6 +174,10 @@ int b200cfd_poisson(b200cfd_handle* h, void* phi, const void* rhs_div, const uin
 /* What the last b200cfd_poisson call did: out4 = {temporal depth used (1 = the one-sweep-per-pass kernels), HBM passes
  * of the temporally blocked kernel (0 if it did not run), bytes per cell one such pass moves, reserved}. */
 int b200cfd_poisson_info(b200cfd_handle* h, int* out4);
+/* keep != 0: the following b200cfd_poisson calls use the SAME, unchanged rhs_div and mask arrays as the previous call (one
+ * solve done in chunks around halo refreshes: the slab solver); the temporally blocked kernel then does not rebuild its
+ * classified copy of the right-hand side per call.  Call with keep = 0 before the right-hand side changes. */
+int b200cfd_poisson_keep_rhs(b200cfd_handle* h, int keep);
 
 /* ---- one export per reference kernel, for unit parity (all device pointers, shape of the handle) ---- */
 /* compute_supg_stabilization_fast (v5.py:149-162) */

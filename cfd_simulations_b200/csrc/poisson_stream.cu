@@ -187,13 +187,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         }
         // column flags as multiplicative masks: owned by this tile AND by this slab (max|dphi| only)
         double ownm[SPL];
-        bool own_lane = true, own_any = false;
 #pragma unroll
         for (int m = 0; m < SPL; ++m) {
             const int c = c0 + m;
             ownm[m] = (c >= x0 && c < x0 + P.OW && c >= P.own0 && c < P.own1 && c < P.nx) ? 1.0 : 0.0;
-            own_lane = own_lane && ownm[m] != 0.0;
-            own_any = own_any || ownm[m] != 0.0;
         }
         // colour of this lane's columns: c0 is a multiple of 4, so cells 0, 2 have the parity of (row + jg0), cells 1, 3 the other
         const int colpar = P.jg0 & 1;
@@ -258,13 +255,9 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                         pn = Rnd<T>::r(pn);
                         if (SPECIAL) pn = sel_int(act, sel_lt(fabs(r[m]), INF, pn, C[m]), C[m]);   // masked / border / inactive: kept
                         out[m] = pn;
-                        // ownership is per lane (window origin, owned width, slab bounds and nx are all multiples of 4) and the
-                        // row test is warp-uniform: one predicate guards a 3-instruction update instead of a multiply and two selects
-                        // (a lane cut by an unaligned slab boundary keeps the per-cell weight)
-                        if (CHECK && rown) {
-                            if (own_lane) ch[k / 2] = fmax(ch[k / 2], fabs(pn - C[m]));
-                            else if (own_any) ch[k / 2] = fmax(ch[k / 2], fabs(pn - C[m]) * ownm[m]);
-                        }
+                        // branch-free on purpose: a per-lane `if (owned)` here diverges inside the pipeline body and cost 25% of the
+                        // tolerance-mode rate when tried (229 -> 172 GLUPS at 8192^2)
+                        if (CHECK) ch[k / 2] = fmax(ch[k / 2], sel_int(rown, fabs(pn - C[m]) * ownm[m], 0.0));
                     };
                     if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
                     else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }

@@ -29,6 +29,9 @@ namespace b200cfd {
 #define MARCH_UNROLL_N(n) MARCH_PRAGMA(unroll n)
 #define MARCH_UNROLL MARCH_UNROLL_N(B200CFD_MARCH_UNROLL)
 #define FPF 6        // L2 prefetch distance of the marching kernels, rows
+#ifndef FIN_LEAN
+#define FIN_LEAN 1   // 0: k_finalize_fast without its lean interior rows (A/B builds)
+#endif
 
 __device__ __forceinline__ void pf_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -353,13 +356,126 @@ __device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0
 // (NPSI == 2: both corrections are pending, the sweep of the second iteration applied the first one only on its load side)
 struct PsiRow { D2 p, q; };
 
+// running maximum of |x|; a NaN never wins (the nanmax of the reference, like fmax) — one compare and a select instead
+// of the NaN-quieting sequence fmax() expands to
+__device__ __forceinline__ void max_abs(double& acc, double x) { const double a = fabs(x); acc = a > acc ? a : acc; }
+
+// The lean rows of k_finalize_fast: the whole 64-column window of the warp lies in interior columns, no flag tile over it
+// carries ibm / mask bits, rows [lo, hi) and the three rows either side of them are interior rows, hi - lo is a multiple of
+// 4 and each lane's two columns are owned together or not at all.  Then BC, IBM and mask do nothing, every guard of the
+// general rows is constant, and what is left is written for the issue slots (the ncu source page of the general loop: 614
+// instructions per lane-row, 150 of them register-rotation moves, 83 fp64 operations):
+//   * rows rotate through register arrays indexed by (row & 3) in a loop unrolled by 4, so rotation is renaming;
+//   * reductions run unweighted per lane and the lane's ownership is applied once after the loop;
+//   * clip / NaN bookkeeping (v5.py:431-438) is one warp vote per row: only a row that holds a value outside
+//     [-vmax, vmax] or a NaN takes the exact per-cell code;
+//   * one prefetch instruction per row covers the four input arrays (lane -> array, 128-byte line).
+// Same operations in the same order per cell as the general rows (shared helpers), so a cell gets the same bits whichever
+// path its warp takes.
+template <typename T, int NPSI>
+__device__ __forceinline__ void finalize_rows_lean(const Geom& g, const double vmax, const T* __restrict__ ua, const T* __restrict__ va,
+                                                   const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u,
+                                                   T* __restrict__ v, const int lo, const int hi, const int c0, const int lane,
+                                                   const bool own, FinAcc& acc) {
+    constexpr bool PSI = NPSI > 0;
+    const bool owner = (unsigned)(lane - 1) < 30u;                   // every column of the window is in bounds here
+    const double i2dx = 1.0 / Rnd<T>::r(g.two_dx), i2dy = 1.0 / Rnd<T>::r(g.two_dy);
+    const double hdx = g.hdx, hdy = g.hdy;
+    const long long pitch = g.pitch;
+    long long ro = (long long)lo * pitch + c0;                       // element offset of (row i, this lane's first column)
+    PsiRow P[4];                                                      // psi rows, slot = (row - lo) & 3
+    D2 SU[2], SV[2], FU[4], FV[4];                                    // stored rows (slot (row - lo) & 1), corrected rows (& 3)
+    auto ldpsi = [&](PsiRow& r, long long off) {
+        if (PSI) r.p = ld2<T>(psi, off);
+        if (NPSI == 2) r.q = ld2<T>(psi1, off);
+    };
+    auto apply = [&](const D2& ur, const D2& vr, const PsiRow& pS, const PsiRow& pC, const PsiRow& pN, D2& fu, D2& fv) {
+        fu = ur; fv = vr;
+        if (PSI) {
+            if (NPSI == 2) {
+                const double qW = shfl_up1(pC.q.y), qE = shfl_dn1(pC.q.x);
+                fu.x = Rnd<T>::r(fu.x - Rnd<T>::r((pC.q.y - qW) * hdx));
+                fv.x = Rnd<T>::r(fv.x - Rnd<T>::r((pN.q.x - pS.q.x) * hdy));
+                fu.y = Rnd<T>::r(fu.y - Rnd<T>::r((qE - pC.q.x) * hdx));
+                fv.y = Rnd<T>::r(fv.y - Rnd<T>::r((pN.q.y - pS.q.y) * hdy));
+            }
+            const double pW = shfl_up1(pC.p.y), pE = shfl_dn1(pC.p.x);
+            fu.x = Rnd<T>::r(fu.x - Rnd<T>::r((pC.p.y - pW) * hdx));
+            fv.x = Rnd<T>::r(fv.x - Rnd<T>::r((pN.p.x - pS.p.x) * hdy));
+            fu.y = Rnd<T>::r(fu.y - Rnd<T>::r((pE - pC.p.x) * hdx));
+            fv.y = Rnd<T>::r(fv.y - Rnd<T>::r((pN.p.y - pS.p.y) * hdy));
+        }
+    };
+    {   // rows lo-1 and lo
+        PsiRow pmm, pm;
+        ldpsi(pmm, ro - 2 * pitch); ldpsi(pm, ro - pitch); ldpsi(P[0], ro); ldpsi(P[1], ro + pitch);
+        const D2 u1 = ld2<T>(ua, ro - pitch), v1 = ld2<T>(va, ro - pitch), u0 = ld2<T>(ua, ro), v0 = ld2<T>(va, ro);
+        apply(u1, v1, pmm, pm, P[0], FU[3], FV[3]);
+        apply(u0, v0, pm, P[0], P[1], FU[0], FV[0]);
+    }
+    SU[1] = ld2<T>(ua, ro + pitch); SV[1] = ld2<T>(va, ro + pitch);
+    ldpsi(P[2], ro + 2 * pitch);
+    // prefetch: lane -> (array, 128-byte line of the window's row); 6 lines cover the 64 columns at any alignment
+    const T* pf;
+    {
+        const int a = min(lane / 6, NPSI + 1), line = lane % 6;
+        const T* base = a == 0 ? ua : a == 1 ? va : a == 2 ? psi : psi1;
+        const int col = min(c0 - 2 * lane + line * (int)(128 / sizeof(T)), g.nx - 1);
+        pf = base + (long long)(lo + FPF) * pitch + col;
+    }
+    double dmax = 0.0, wmax = 0.0, e = 0.0, mu = 0.0, mv = 0.0;
+    unsigned cnt = 0, bad = 0;
+    for (int i4 = lo; i4 < hi; i4 += 4) {
+        const bool more = i4 + 4 < hi;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (k < 3 || more) {                                      // stored row i+2, psi row i+3
+                SU[k & 1] = ld2<T>(ua, ro + 2 * pitch); SV[k & 1] = ld2<T>(va, ro + 2 * pitch);
+                ldpsi(P[(k + 3) & 3], ro + 3 * pitch);
+            }
+            if (i4 + k + FPF < g.ny) pf_l2(pf);
+            pf += pitch;
+            apply(SU[(k + 1) & 1], SV[(k + 1) & 1], P[k], P[(k + 1) & 3], P[(k + 2) & 3], FU[(k + 1) & 3], FV[(k + 1) & 3]);
+            const D2 fuc = FU[k], fvc = FV[k], fum = FU[(k + 3) & 3], fvm = FV[(k + 3) & 3], fun = FU[(k + 1) & 3], fvn = FV[(k + 1) & 3];
+            const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), fvW = shfl_up1(fvc.y), fvE = shfl_dn1(fvc.x);
+            const double Dx = Rnd<T>::r((fuc.y - fuW) * hdx + (fvn.x - fvm.x) * hdy);
+            const double Dy = Rnd<T>::r((fuE - fuc.x) * hdx + (fvn.y - fvm.y) * hdy);
+            max_abs(dmax, Dx); max_abs(dmax, Dy);
+            const double Wx = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvc.y - fvW) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.x - fum.x) * i2dy));
+            const double Wy = Rnd<T>::r(Rnd<T>::r(Rnd<T>::r(fvE - fvc.x) * i2dx) - Rnd<T>::r(Rnd<T>::r(fun.y - fum.y) * i2dy));
+            max_abs(wmax, Wx); max_abs(wmax, Wy);
+            const double ex = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.x * fuc.x) + Rnd<T>::r(fvc.x * fvc.x)));
+            const double ey = Rnd<T>::r(0.5 * Rnd<T>::r(Rnd<T>::r(fuc.y * fuc.y) + Rnd<T>::r(fvc.y * fvc.y)));
+            const bool odd = !(fabs(fuc.x) <= vmax) || !(fabs(fuc.y) <= vmax) || !(fabs(fvc.x) <= vmax) || !(fabs(fvc.y) <= vmax);
+            if (!__any_sync(0xffffffffu, odd)) {
+                if (owner) { st2<T>(u, ro, fuc.x, fuc.y); st2<T>(v, ro, fvc.x, fvc.y); }
+                e += ex; e += ey; cnt += 2;
+                max_abs(mu, fuc.x); max_abs(mu, fuc.y); max_abs(mv, fvc.x); max_abs(mv, fvc.y);
+            } else {
+                const double cux = fmin(fmax(fuc.x, -vmax), vmax), cuy = fmin(fmax(fuc.y, -vmax), vmax);
+                const double cvx = fmin(fmax(fvc.x, -vmax), vmax), cvy = fmin(fmax(fvc.y, -vmax), vmax);
+                if (owner) {     // np.clip propagates NaN; fmin/fmax would drop it
+                    st2<T>(u, ro, fuc.x == fuc.x ? cux : fuc.x, fuc.y == fuc.y ? cuy : fuc.y);
+                    st2<T>(v, ro, fvc.x == fvc.x ? cvx : fvc.x, fvc.y == fvc.y ? cvy : fvc.y);
+                }
+                if (ex == ex) { e += ex; cnt += 1; }
+                if (ey == ey) { e += ey; cnt += 1; }
+                bad |= (!isfinite(fuc.x) || !isfinite(fvc.x) || !isfinite(fuc.y) || !isfinite(fvc.y)) ? 1u : 0u;
+                max_abs(mu, cux); max_abs(mu, cuy); max_abs(mv, cvx); max_abs(mv, cvy);
+            }
+            ro += pitch;
+        }
+    }
+    if (own) { acc.dmax = dmax; acc.wmax = wmax; acc.e = e; acc.cnt = cnt; acc.bad = bad; acc.mu = mu; acc.mv = mv; }
+}
+
 template <typename T, int NPSI>
 __global__ void __launch_bounds__(FBT, 3)
 k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
                 const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u, T* __restrict__ v,
                 const double* __restrict__ ibm, const uint8_t* __restrict__ mask, const double* __restrict__ y,
                 double* __restrict__ ke_part, unsigned long long* __restrict__ cnt_part, const uint8_t* __restrict__ flags,
-                int ntx, int rpb, int bx_cut, int bx_off_a, int bx_off_b, int nbx_total) {
+                int ntx, int rpb, int bx_cut, int bx_off_a, int bx_off_b, int nbx_total, int lean_on) {
     constexpr bool PSI = NPSI > 0;
     pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -389,6 +505,12 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
         // reduction weights: interior cells of the owned columns (divergence, vorticity) / owned columns (energy, maxima)
         const double wdx = (inx && ownx) ? 1.0 : 0.0, wdy = (iny && owny) ? 1.0 : 0.0, wox = ownx ? 1.0 : 0.0, woy = owny ? 1.0 : 0.0;
         const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+        // the lean rows (see finalize_rows_lean): a warp-uniform choice
+        const bool lean = FIN_LEAN && lean_on && !has_ibm && !has_mask && r0 >= 2 && r1 + 3 <= g.ny && ((r1 - r0) & 3) == 0 &&
+                          __all_sync(0xffffffffu, inx && iny && ownx == owny);
+        if (lean) {
+            finalize_rows_lean<T, NPSI>(g, p.max_velocity, ua, va, psi, psi1, u, v, lo, hi, c0, lane, ownx, acc);
+        } else {
         // wall rows: u = v = 0 (v5.py:357-360); they count in the energy mean
         if (owner && r0 == 0) { st2<T>(u, c0, 0.0, 0.0); st2<T>(v, c0, 0.0, 0.0); acc.cnt += (ownx ? 1 : 0) + (owny ? 1 : 0); }
         if (owner && r1 == g.ny) {
@@ -527,6 +649,7 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
                 pm = pc; pc = pn; pn = pn2; urn = urn2; vrn = vrn2;
             }
         }
+        }   // general rows
     }
     finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * nbx_total + bx);
 }
@@ -577,7 +700,8 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
     if (part == 1) { grid.x = bl + (nbx - br); cut = bl; off_a = 0; off_b = br - bl; }        // edges: [0, bl) and [br, nbx)
     else if (part == 2) { grid.x = br - bl; cut = nbx; off_a = bl; }                            // interior: [bl, br)
     if (grid.x == 0) return;
-#define FF(T, NP) launch_pdl(k_finalize_fast<T, NP>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (const T*)psi1, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb, cut, off_a, off_b, nbx)
+#define FF(T, NP) launch_pdl(k_finalize_fast<T, NP>, grid, dim3(FBT), s, g, p, ctl, (const T*)ua, (const T*)va, (const T*)psi, (const T*)psi1, (T*)u, (T*)v, ibm, mask, y, ke_partials, cnt_partials, flags, ntx, rpb, cut, off_a, off_b, nbx, lean_on)
+    static const int lean_on = getenv("B200CFD_FIN_LEAN") ? atoi(getenv("B200CFD_FIN_LEAN")) : 1;   // developer knob (A/B)
     if (dtype == 0) { if (np == 2) FF(double, 2); else if (np == 1) FF(double, 1); else FF(double, 0); }
     else { if (np == 2) FF(float, 2); else if (np == 1) FF(float, 1); else FF(float, 0); }
 #undef FF

@@ -3,10 +3,12 @@ missing every compute entry point raises."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "libb200cfd.so"
+# B200CFD_LIB: developer knob, an A/B build of the same library (tools/build_variant.sh)
+LIB_PATH = Path(os.environ["B200CFD_LIB"]).resolve() if os.environ.get("B200CFD_LIB") else PKG / "libb200cfd.so"
 
 F64, F32 = 0, 1
 POISSON_AS_EXECUTED, POISSON_AS_WRITTEN, POISSON_JACOBI, POISSON_SOR_V2 = 0, 1, 2, 3

@@ -12,6 +12,7 @@
 // red-black iteration), :349-360 (BC), :228-237 (IBM), :421-438 (diagnostics, clip).
 #include "kernels.h"
 #include <cstdlib>
+#include <type_traits>
 #include "cellmath.cuh"
 
 namespace b200cfd {
@@ -29,6 +30,9 @@ namespace b200cfd {
 #define MARCH_UNROLL_N(n) MARCH_PRAGMA(unroll n)
 #define MARCH_UNROLL MARCH_UNROLL_N(B200CFD_MARCH_UNROLL)
 #define FPF 6        // L2 prefetch distance of the marching kernels, rows
+#ifndef FIN_MINB
+#define FIN_MINB 3   // resident blocks per SM the finalize kernel is compiled for
+#endif
 #ifndef FIN_LEAN
 #define FIN_LEAN 1   // 0: k_finalize_fast without its lean interior rows (A/B builds)
 #endif
@@ -470,7 +474,7 @@ __device__ __forceinline__ void finalize_rows_lean(const Geom& g, const double v
 }
 
 template <typename T, int NPSI>
-__global__ void __launch_bounds__(FBT, 3)
+__global__ void __launch_bounds__(FBT, FIN_MINB)
 k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__ ua, const T* __restrict__ va,
                 const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u, T* __restrict__ v,
                 const double* __restrict__ ibm, const uint8_t* __restrict__ mask, const double* __restrict__ y,
@@ -716,11 +720,136 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
 // phi of rows i-2, i-1, i in registers; the correction of row i-1 is applied as soon as phi of row i exists.  A block
 // of rows [r0, r1) computes phi of rows r0-1 and r1 redundantly (they belong to the neighbouring blocks).
 // ------------------------------------------------------------------------------------------------
+// The lean rows of k_div_rb1_correct_fast (same idea as finalize_rows_lean): the warp's whole 64-column window lies in
+// interior columns, no flag tile over it carries a mask bit, rows [lo-3, hi+3) are interior rows of the array, hi - lo is a
+// multiple of 4, each lane's two columns are owned together or not at all.  What the general rows spend on guards, clamps,
+// per-cell selects and register rotation (365 instructions per lane-row for 48 fp64 operations) goes away:
+//   * rows rotate through register arrays indexed by (row & 3) in a loop unrolled by 4, the colour of each row is a
+//     compile-time constant of the unrolled body (two instances of the loop, one per colour of row lo);
+//   * phi of an odd cell, (D/dt_c) d, is computed ONCE per cell: it is that cell's final value and the north / south
+//     neighbour of the even cells above and below (the general rows evaluate it three times);
+//   * the two halo lanes fetch their outer u* neighbour with one predicated load per row;
+//   * reductions run unweighted per lane, ownership is applied once after the loop.
+// Per cell the operations and their order are those of the general rows, so a cell gets the same bits on either path.
+__device__ __forceinline__ void max_pos(double& acc, double x) { acc = x > acc ? x : acc; }
+
+template <typename T, bool DIV>
+__device__ __forceinline__ void div_rb1_correct_rows_lean(const Geom& g, const T* __restrict__ us, const T* __restrict__ vs,
+                                                          T* __restrict__ phi, T* __restrict__ div_out, T* __restrict__ ua,
+                                                          T* __restrict__ va, const double inv_dt, const double dt, const int lo,
+                                                          const int hi, const int c0, const int lane, const bool own,
+                                                          double& dabs_o, double& ch_o, double& gmax_o) {
+    const bool owner = (unsigned)(lane - 1) < 30u;
+    const bool halo_lane = lane == 0 || lane == 31;
+    const long long pitch = g.pitch;
+    const double hdx = g.hdx, hdy = g.hdy;
+    long long ro = (long long)lo * pitch + c0;                       // element offset of (row j, this lane's first column)
+    const T* __restrict__ hp = us + (lane == 0 ? -1 : 2);            // + ro: the outer x-neighbour of a halo lane
+    auto halo = [&](long long off) { return halo_lane ? ld(hp, off) : 0.0; };
+    // D of one row from its u* pair (x-neighbours by shuffle, the halo lanes' outer one from `h`) and v* of the rows N, S
+    auto drow = [&](const D2& uc, const double h, const D2& vN, const D2& vS) {
+        double uW = shfl_up1(uc.y), uE = shfl_dn1(uc.x);
+        uW = lane == 0 ? h : uW;
+        uE = lane == 31 ? h : uE;
+        D2 d;
+        d.x = div_raw<T>(g, uc.y, uW, vN.x, vS.x);
+        d.y = div_raw<T>(g, uE, uc.x, vN.y, vS.y);
+        return d;
+    };
+    // final phi of a row: po = phi of its odd cell, pn / ps = phi of the (odd) cells north / south of its even cell
+    auto final_row = [&](const bool xe, const double po, const double pn, const double ps, const D2& Dc) {
+        D2 q;
+        if (xe) {
+            const double pW = shfl_up1(po);
+            q.y = po;
+            q.x = Rnd<T>::r((g.ax * (po + pW) + g.ay * (pn + ps) - (-Dc.x * inv_dt)) * g.dinv);
+        } else {
+            const double pE = shfl_dn1(po);
+            q.x = po;
+            q.y = Rnd<T>::r((g.ax * (pE + po) + g.ay * (pn + ps) - (-Dc.y * inv_dt)) * g.dinv);
+        }
+        return q;
+    };
+    double dabs = 0.0, ch = 0.0, gmax = 0.0;
+    auto run = [&](auto XE_LO) {
+        constexpr bool xe_lo = decltype(XE_LO)::value;               // the .x cells of row lo are the even (black) ones
+        D2 U[4], V[4], PH[4], DS[2];                                 // slots: u*, v* (row - lo) & 3; phi (row - lo + 1) & 3; D (row - lo) & 1
+        double HL[2], PO[2];                                         // halo-lane neighbour, phi of the odd cell: (row - lo) & 1
+        {   // rows lo-2 .. lo+1: D and the odd cells' phi; phi of rows lo-1 and lo
+            const D2 vm3 = ld2<T>(vs, ro - 3 * pitch), vm2 = ld2<T>(vs, ro - 2 * pitch), vm1 = ld2<T>(vs, ro - pitch);
+            V[0] = ld2<T>(vs, ro); V[1] = ld2<T>(vs, ro + pitch); V[2] = ld2<T>(vs, ro + 2 * pitch);
+            const D2 um2 = ld2<T>(us, ro - 2 * pitch), um1 = ld2<T>(us, ro - pitch);
+            U[0] = ld2<T>(us, ro); U[1] = ld2<T>(us, ro + pitch);
+            const double hm2 = halo(ro - 2 * pitch), hm1 = halo(ro - pitch), h0 = halo(ro), h1 = halo(ro + pitch);
+            const D2 Dm2 = drow(um2, hm2, vm1, vm3), Dm1 = drow(um1, hm1, V[0], vm2), D0 = drow(U[0], h0, V[1], vm1);
+            DS[1] = drow(U[1], h1, V[2], V[0]);
+            // row parity: lo-2 and lo as xe_lo, lo-1 and lo+1 the other colour
+            const double pom2 = phi_odd<T>(g, xe_lo ? Dm2.y : Dm2.x, inv_dt), pom1 = phi_odd<T>(g, xe_lo ? Dm1.x : Dm1.y, inv_dt);
+            const double po0 = phi_odd<T>(g, xe_lo ? D0.y : D0.x, inv_dt);
+            PO[1] = phi_odd<T>(g, xe_lo ? DS[1].x : DS[1].y, inv_dt);
+            PH[0] = final_row(!xe_lo, pom1, po0, pom2, Dm1);
+            PH[1] = final_row(xe_lo, po0, PO[1], xe_lo ? PH[0].x : PH[0].y, D0);
+            if (owner) {
+                st2<T>(phi, ro, PH[1].x, PH[1].y);
+                if (DIV) st2<T>(div_out, ro, D0.x, D0.y);
+            }
+            max_abs(dabs, D0.x); max_abs(dabs, D0.y); max_abs(ch, PH[1].x); max_abs(ch, PH[1].y);
+        }
+        U[2] = ld2<T>(us, ro + 2 * pitch); HL[0] = halo(ro + 2 * pitch); V[3] = ld2<T>(vs, ro + 3 * pitch);
+        const T* pf = (lane < 6 ? us : vs) + (long long)(lo + FPF) * pitch + min(c0 - 2 * lane + (lane % 6) * (int)(128 / sizeof(T)), g.nx - 1);
+        for (int j4 = lo; j4 < hi; j4 += 4) {
+            const bool more = j4 + 4 < hi;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const bool xe_j1 = (k & 1) ? xe_lo : !xe_lo;         // colour of row j+1 (row j+2: the other one)
+                const D2 vk = V[k];                                  // v*(j): its slot takes v*(j+4)
+                if (k < 3 || more) {
+                    V[k] = ld2<T>(vs, ro + 4 * pitch);
+                    U[(k + 3) & 3] = ld2<T>(us, ro + 3 * pitch);
+                    HL[(k + 1) & 1] = halo(ro + 3 * pitch);
+                }
+                if (lane < 12 && j4 + k + FPF < g.ny) pf_l2(pf);
+                pf += pitch;
+                // D(j+2), phi of its odd cell
+                const D2 D2n = drow(U[(k + 2) & 3], HL[k & 1], V[(k + 3) & 3], V[(k + 1) & 3]);
+                const double po2 = phi_odd<T>(g, xe_j1 ? D2n.x : D2n.y, inv_dt);
+                // final phi(j+1)
+                const D2 D1 = DS[(k + 1) & 1];
+                const D2 pj = PH[(k + 1) & 3];
+                const D2 pc = final_row(xe_j1, PO[(k + 1) & 1], po2, xe_j1 ? pj.x : pj.y, D1);
+                PH[(k + 2) & 3] = pc; DS[k & 1] = D2n; PO[k & 1] = po2;
+                if (k < 3 || more) {
+                    if (owner) {
+                        st2<T>(phi, ro + pitch, pc.x, pc.y);
+                        if (DIV) st2<T>(div_out, ro + pitch, D1.x, D1.y);
+                    }
+                    max_abs(dabs, D1.x); max_abs(dabs, D1.y); max_abs(ch, pc.x); max_abs(ch, pc.y);
+                }
+                // correction of row j from phi rows j-1, j, j+1
+                const D2 pmm = PH[k];
+                const double pW = shfl_up1(pj.y), pE = shfl_dn1(pj.x);
+                const double gxx = Rnd<T>::r((pj.y - pW) * hdx), gyx = Rnd<T>::r((pc.x - pmm.x) * hdy);
+                const double gxy = Rnd<T>::r((pE - pj.x) * hdx), gyy = Rnd<T>::r((pc.y - pmm.y) * hdy);
+                if (owner) {
+                    st2<T>(ua, ro, axmy<T>(U[k].x, dt, gxx), axmy<T>(U[k].y, dt, gxy));
+                    st2<T>(va, ro, axmy<T>(vk.x, dt, gyx), axmy<T>(vk.y, dt, gyy));
+                }
+                max_pos(gmax, Rnd<T>::r(Rnd<T>::r(gxx * gxx) + Rnd<T>::r(gyx * gyx)));
+                max_pos(gmax, Rnd<T>::r(Rnd<T>::r(gxy * gxy) + Rnd<T>::r(gyy * gyy)));
+                ro += pitch;
+            }
+        }
+    };
+    if (((lo + g.jg0 + c0) & 1) == 0) run(std::true_type{}); else run(std::false_type{});
+    if (own) { dabs_o = dabs; ch_o = ch; gmax_o = gmax; }
+}
+
 template <typename T, bool DIV>
 __global__ void __launch_bounds__(FBT, 4)
 k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ vs, const uint8_t* __restrict__ mask,
                        T* __restrict__ phi, T* __restrict__ div_out, T* __restrict__ ua, T* __restrict__ va,
-                       double inv_dt, StepCtl* __restrict__ ctl, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+                       double inv_dt, StepCtl* __restrict__ ctl, const uint8_t* __restrict__ flags, int ntx, int rpb,
+                       int lean_on) {
     pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
@@ -742,6 +871,11 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
         const bool ownx = owner && c0 >= g.own0 && c0 < g.own1, owny = owner && c0 + 1 >= g.own0 && c0 + 1 < g.own1;
         const double dt = ctl->dt;
         const int lo = max(r0, 1), hi = min(r1, g.ny - 1);
+        const bool lean = lean_on && !has_mask && r0 >= 3 && r1 + 3 <= g.ny && ((r1 - r0) & 3) == 0 &&
+                          __all_sync(0xffffffffu, xin && yin && ownx == owny);
+        if (lean) {
+            div_rb1_correct_rows_lean<T, DIV>(g, us, vs, phi, div_out, ua, va, inv_dt, dt, lo, hi, c0, lane, ownx, dabs, ch, gmax);
+        } else {
         // wall rows: D = phi = 0, no gradient: ua = u*, va = v*
         if (owner && r0 == 0) {
             st2<T>(phi, c0, 0.0, 0.0); if (DIV) st2<T>(div_out, c0, 0.0, 0.0);
@@ -843,6 +977,7 @@ k_div_rb1_correct_fast(Geom g, const T* __restrict__ us, const T* __restrict__ v
                 p_mm = p_m; p_m = p_c; mm = mc; mc = mn; mn = mn2;
             }
         }
+        }   // general rows
     }
     if (ctl) {
         block_atomic_max3(dabs, ch, sqrt(gmax), &ctl->max_div_pre, &ctl->pois_change, &ctl->max_grad);
@@ -861,7 +996,8 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
     rpb = pick_rpb(bx, g.ny, 4 * n_sm, 4, rpb);              // k_div_rb1_correct_fast: 4 blocks per SM
     const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define DCF(T, DIV) launch_pdl(k_div_rb1_correct_fast<T, DIV>, grid, dim3(FBT), s, g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb)
+#define DCF(T, DIV) launch_pdl(k_div_rb1_correct_fast<T, DIV>, grid, dim3(FBT), s, g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb, lean_on)
+    static const int lean_on = getenv("B200CFD_K23_LEAN") ? atoi(getenv("B200CFD_K23_LEAN")) : 1;   // developer knob (A/B)
     if (dtype == 0) { if (div_out) DCF(double, true); else DCF(double, false); }
     else { if (div_out) DCF(float, true); else DCF(float, false); }
 #undef DCF

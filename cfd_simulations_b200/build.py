@@ -14,7 +14,7 @@ CSRC = PKG / "csrc"
 OBJ = PKG / "build"
 LIB = PKG / "libb200cfd.so"
 SOURCES = ["step_kernels.cu", "step_fast.cu", "poisson.cu", "poisson_tb.cu", "poisson_stream.cu", "cleandiv.cu", "cleandiv_tma.cu", "finalize_tma.cu", "euler.cu",
-           "halo.cu", "c_api.cu"]
+           "halo.cu", "static_scratch.cu", "c_api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
 
 

@@ -70,6 +70,8 @@ struct b200cfd_handle {
     std::string err;
 };
 
+namespace b200cfd { void set_global_error(const char* msg) { g_create_error = msg; } }
+
 static int fail(b200cfd_handle* h, int code, const char* fmt, ...) {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);

@@ -134,4 +134,7 @@ bool launch_clean_sweep_tma(int dtype, const Geom& g, const CleanPlan& cp, const
 int clean_sweep_launches(const CleanPlan& cp);   // kernels one launch_clean_sweep enqueues (2 with the two-pass plan)
 void launch_clean_apply(int dtype, const Geom& g, void* u, void* v, const void* psi, cudaStream_t s);
 
+// message returned by b200cfd_last_error(NULL) on this thread (c_api.cu), for entry points that have no handle
+void set_global_error(const char* msg);
+
 }  // namespace b200cfd

@@ -206,6 +206,22 @@ int b200cfd_k_clean_divergence(b200cfd_handle* h, void* u, void* v, int iteratio
 int b200cfd_k_predictor(b200cfd_handle* h, const void* u, const void* v, void* u_star, void* v_star,
                         void* tau_or_null, const double* ibm, const double* y, int64_t step, double dt, void* stream);
 
+/* ---- allocation-free entry point ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * `sweeps` Jacobi sweeps of solve_pressure_fast (the arithmetic of b200cfd_poisson with mode = JACOBI, temporal_depth = 1)
+ * on dense row-major (ny, nx) device arrays of the CURRENT device: phi in/out (not zeroed here), rhs_div = div_u_star,
+ * mask may be NULL.  dtype = B200CFD_F64 / B200CFD_F32.  Needs no handle and calls no cudaMalloc / cudaFree / allocating
+ * library routine: the ping-pong buffer is a file-scope device array of B200CFD_STATIC_SCRATCH_BYTES that every GPU which
+ * loads the library holds until the process exits.  ny * nx * sizeof(element) beyond that size is rejected with
+ * B200CFD_EINVAL (b200cfd_last_error(NULL) says so); use b200cfd_poisson there.  All calls on a device share the array and
+ * it keeps the last call's contents (nothing in it has to start at zero: a call's first sweep writes every cell it later
+ * reads); calls that overlap on the GPU (different streams, no ordering between them) race on it.  Asynchronous on
+ * `stream`. */
+#define B200CFD_STATIC_SCRATCH_BYTES (8u << 20)   /* 8 MiB: 1024 x 1024 fp64 cells, 2048 x 1024 fp32 cells */
+int b200cfd_jacobi_static(int dtype, int ny, int nx, void* phi, const void* rhs_div, const uint8_t* mask,
+                          double dx, double dt, int sweeps, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

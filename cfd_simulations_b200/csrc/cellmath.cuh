@@ -245,6 +245,36 @@ __device__ __forceinline__ void finalize_block_reduce(const FinAcc& a, StepCtl* 
     }
 }
 
+// The same for 1-D blocks with ONE barrier instead of thirteen: every warp reduces its seven values with shuffles and
+// leaves them in shared memory, warp 0 folds the warps.  The energy and count sums use the tree of block_sum (warp_sum of
+// the lanes, then warp_sum of the per-warp values padded with zeros), so the partial a block writes has the same bits.
+__device__ __forceinline__ void finalize_block_reduce1(const FinAcc& a, StepCtl* __restrict__ ctl, double* __restrict__ ke_part,
+                                                       unsigned long long* __restrict__ cnt_part, int block_id) {
+    __shared__ double s_r[6][32];
+    __shared__ unsigned s_bad[32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    const double m0 = warp_max(a.dmax), m1 = warp_max(a.wmax), m2 = warp_max(a.mu), m3 = warp_max(a.mv);
+    const double e = warp_sum(a.e), c = warp_sum((double)a.cnt);
+    const unsigned bad = __any_sync(0xffffffffu, a.bad != 0) ? 1u : 0u;
+    if (lane == 0) { s_r[0][w] = m0; s_r[1][w] = m1; s_r[2][w] = m2; s_r[3][w] = m3; s_r[4][w] = e; s_r[5][w] = c; s_bad[w] = bad; }
+    __syncthreads();
+    if (w != 0) return;
+    const bool in = lane < nw;
+    const double M0 = warp_max(in ? s_r[0][lane] : 0.0), M1 = warp_max(in ? s_r[1][lane] : 0.0);
+    const double M2 = warp_max(in ? s_r[2][lane] : 0.0), M3 = warp_max(in ? s_r[3][lane] : 0.0);
+    const double E = warp_sum(in ? s_r[4][lane] : 0.0), Cn = warp_sum(in ? s_r[5][lane] : 0.0);
+    const bool nbad = __any_sync(0xffffffffu, in && s_bad[lane] != 0);
+    if (lane == 0) {
+        if (M0 > 0.0) atomicMax(&ctl->max_div_post, (unsigned long long)__double_as_longlong(M0));
+        if (M1 > 0.0) atomicMax(&ctl->max_vort, (unsigned long long)__double_as_longlong(M1));
+        if (M2 > 0.0) atomicMax(&ctl->max_u, (unsigned long long)__double_as_longlong(M2));
+        if (M3 > 0.0) atomicMax(&ctl->max_v, (unsigned long long)__double_as_longlong(M3));
+        ke_part[block_id] = E;
+        cnt_part[block_id] = (unsigned long long)(Cn + 0.5);
+        if (nbad) atomicOr(&ctl->nonfinite, 1u);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K2 at one cell, any position: D = div(u*, v*) and exactly ONE red-black iteration from phi = 0 ("as executed",
 // SURVEY finding 3).  Odd cells: phi = (D/dt_c) d.  Even cells: phi = (a(pE+pW) + b(pN+pS) + D/dt_c) d with the four

@@ -33,6 +33,9 @@ namespace b200cfd {
 #ifndef FIN_MINB
 #define FIN_MINB 3   // resident blocks per SM the finalize kernel is compiled for
 #endif
+#ifndef FIN_DEEP
+#define FIN_DEEP 0   // lean finalize rows: 1 = loads issued two rows ahead; measured: no gain (60.2 vs 59.8 us at 4096x1024, 2.23 vs 2.20 ms at 16384^2)
+#endif
 #ifndef FIN_LEAN
 #define FIN_LEAN 1   // 0: k_finalize_fast without its lean interior rows (A/B builds)
 #endif
@@ -419,6 +422,10 @@ __device__ __forceinline__ void finalize_rows_lean(const Geom& g, const double v
     }
     SU[1] = ld2<T>(ua, ro + pitch); SV[1] = ld2<T>(va, ro + pitch);
     ldpsi(P[2], ro + 2 * pitch);
+    if (FIN_DEEP) {      // two rows of loads in flight per warp: an L2 hit takes longer than one row of this loop
+        SU[0] = ld2<T>(ua, ro + 2 * pitch); SV[0] = ld2<T>(va, ro + 2 * pitch);
+        ldpsi(P[3], ro + 3 * pitch);
+    }
     // prefetch: lane -> (array, 128-byte line of the window's row); 6 lines cover the 64 columns at any alignment
     const T* pf;
     {
@@ -433,13 +440,17 @@ __device__ __forceinline__ void finalize_rows_lean(const Geom& g, const double v
         const bool more = i4 + 4 < hi;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            if (k < 3 || more) {                                      // stored row i+2, psi row i+3
+            if (!FIN_DEEP && (k < 3 || more)) {                       // stored row i+2, psi row i+3
                 SU[k & 1] = ld2<T>(ua, ro + 2 * pitch); SV[k & 1] = ld2<T>(va, ro + 2 * pitch);
                 ldpsi(P[(k + 3) & 3], ro + 3 * pitch);
             }
             if (i4 + k + FPF < g.ny) pf_l2(pf);
             pf += pitch;
             apply(SU[(k + 1) & 1], SV[(k + 1) & 1], P[k], P[(k + 1) & 3], P[(k + 2) & 3], FU[(k + 1) & 3], FV[(k + 1) & 3]);
+            if (FIN_DEEP && (k < 2 || more)) {                        // stored row i+3, psi row i+4 into the slots apply() just freed
+                SU[(k + 1) & 1] = ld2<T>(ua, ro + 3 * pitch); SV[(k + 1) & 1] = ld2<T>(va, ro + 3 * pitch);
+                ldpsi(P[k], ro + 4 * pitch);
+            }
             const D2 fuc = FU[k], fvc = FV[k], fum = FU[(k + 3) & 3], fvm = FV[(k + 3) & 3], fun = FU[(k + 1) & 3], fvn = FV[(k + 1) & 3];
             const double fuW = shfl_up1(fuc.y), fuE = shfl_dn1(fuc.x), fvW = shfl_up1(fvc.y), fvE = shfl_dn1(fvc.x);
             const double Dx = Rnd<T>::r((fuc.y - fuW) * hdx + (fvn.x - fvm.x) * hdy);
@@ -655,7 +666,7 @@ k_finalize_fast(Geom g, Phys p, StepCtl* __restrict__ ctl, const T* __restrict__
         }
         }   // general rows
     }
-    finalize_block_reduce(acc, ctl, ke_part, cnt_part, blockIdx.y * nbx_total + bx);
+    finalize_block_reduce1(acc, ctl, ke_part, cnt_part, blockIdx.y * nbx_total + bx);
 }
 
 void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,

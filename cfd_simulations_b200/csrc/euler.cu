@@ -55,12 +55,13 @@ struct StepParams {
 
 struct Acc { double sx, sy; unsigned nan; };
 
+template <bool EXACT>
 __device__ __forceinline__ void put(float4* __restrict__ out, const uint8_t* __restrict__ wedge, size_t idx, float4 q,
                                     const Phys& P, Acc& acc) {
     if (wedge[idx]) { q.y = 0.f; q.z = 0.f; }                       // :312-313
     out[idx] = q;
     double sx, sy;
-    cell_speeds(q, P, sx, sy);
+    cell_speeds<EXACT>(q, P, sx, sy);
     acc.nan |= (q.x != q.x) | (q.y != q.y) | (q.z != q.z) | (q.w != q.w) | (sx != sx) | (sy != sy);
     acc.sx = fmax(acc.sx, sx);
     acc.sy = fmax(acc.sy, sy);
@@ -68,14 +69,15 @@ __device__ __forceinline__ void put(float4* __restrict__ out, const uint8_t* __r
 
 // One cell of row i after update_state, through the y-boundary part of apply_boundary_conditions (:284-289):
 // flip the reflective prefix, then (if any column is not reflective) copy into the two border columns.
+template <bool EXACT>
 __device__ __forceinline__ void emit(float4* __restrict__ out, const uint8_t* __restrict__ wedge, const StepParams& S,
                                      int i, int c, float4 q, Acc& acc) {
     if (c < S.n_reflect) q.z = -q.z;
     const size_t row = (size_t)i * S.ny;
-    put(out, wedge, row + c, q, S.phys, acc);
+    put<EXACT>(out, wedge, row + c, q, S.phys, acc);
     if (S.n_reflect < S.ny) {
-        if (c == 1) put(out, wedge, row, q, S.phys, acc);
-        if (c == S.ny - 2) put(out, wedge, row + S.ny - 1, q, S.phys, acc);
+        if (c == 1) put<EXACT>(out, wedge, row, q, S.phys, acc);
+        if (c == S.ny - 2) put<EXACT>(out, wedge, row + S.ny - 1, q, S.phys, acc);
     }
 }
 
@@ -113,7 +115,7 @@ k_euler_step(const StepParams S, const float4* __restrict__ in, float4* __restri
     const double ax = dt / S.dx, ay = dt / S.dy;
     Acc acc = {0.0, 0.0, 0u};
 
-    if (writes && chunk == 0 && S.inflow_row >= 0) emit(out, wedge, S, S.inflow_row, c, S.fs, acc);   // :279-282
+    if (writes && chunk == 0 && S.inflow_row >= 0) emit<EXACT>(out, wedge, S, S.inflow_row, c, S.fs, acc);   // :279-282
 
     const float4* col = in + cc;
     float4 qN = __ldg(col + (size_t)(r0 + 1) * S.ny);
@@ -121,19 +123,19 @@ k_euler_step(const StepParams S, const float4* __restrict__ in, float4* __restri
     float4 Fw;
     {
         const Cell W = make_cell<EXACT>(__ldg(col + (size_t)(r0 - 1) * S.ny), P);
-        Fw = face_flux<SOLVER, true>(W, C, P);
+        Fw = face_flux<SOLVER, true, EXACT>(W, C, P);
     }
     for (int i = r0; i <= r1; ++i) {
         const float4 qNN = __ldg(col + (size_t)min(i + 2, S.nx - 1) * S.ny);   // next iteration's row, in flight during the math
         const Cell N = make_cell<EXACT>(qN, P);
-        const float4 Fe = face_flux<SOLVER, true>(C, N, P);                     // x-face (i | i+1)
+        const float4 Fe = face_flux<SOLVER, true, EXACT>(C, N, P);                     // x-face (i | i+1)
         const Cell Y = shfl_down_cell<SOLVER>(C);                               // cell (i, c+1)
-        const float4 Gn = face_flux<SOLVER, false>(C, Y, P);                    // y-face (c | c+1)
+        const float4 Gn = face_flux<SOLVER, false, EXACT>(C, Y, P);                    // y-face (c | c+1)
         const float4 Gs = shfl_up4(Gn);                                         // y-face (c-1 | c)
         if (writes) {
             const float4 q = update_cell(C.U, Fw, Fe, Gs, Gn, ax, ay, P);
-            emit(out, wedge, S, i, c, q, acc);
-            if (i + 1 == S.outflow_row) emit(out, wedge, S, S.outflow_row, c, q, acc);            // :283
+            emit<EXACT>(out, wedge, S, i, c, q, acc);
+            if (i + 1 == S.outflow_row) emit<EXACT>(out, wedge, S, S.outflow_row, c, q, acc);            // :283
         }
         Fw = Fe;
         C = N;

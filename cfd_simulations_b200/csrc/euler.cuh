@@ -24,6 +24,28 @@ struct Cell {
 
 __device__ __forceinline__ double clipd(double x, double lo, double hi) { return fmax(lo, fmin(x, hi)); }
 
+// Reciprocal and square root for the default (not exact_division) mode: the hardware seed (MUFU.RCP64H / RSQ64H, about 20
+// bits) and two Newton steps, 5 / 9 instructions with no slow path, against ~30 each (plus a call for the special cases)
+// for the IEEE-rounded operations.  Accurate to 1-2 ulp of a double; every consumer rounds to float32 afterwards.
+// Denominators here are positive and far from the subnormal range (the reference adds eps to each of them).
+__device__ __forceinline__ double rcp_fast(double b) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(b));
+    double e = fma(-b, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-b, r, 1.0);
+    return fma(r, e, r);
+}
+__device__ __forceinline__ double sqrt_fast(double x) {      // x > 0
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    y = y * fma(-(hx * y), y, 1.5);
+    y = y * fma(-(hx * y), y, 1.5);
+    return x * y;
+}
+template <bool EXACT> __device__ __forceinline__ double dv(double a, double b) { return EXACT ? a / b : a * rcp_fast(b); }
+
 // EXACT: IEEE divisions where the reference divides (bit-faithful); otherwise one reciprocal per cell.
 template <bool EXACT>
 __device__ __forceinline__ Cell make_cell(const float4 q, const Phys& P) {
@@ -39,13 +61,13 @@ __device__ __forceinline__ Cell make_cell(const float4 q, const Phys& P) {
         pr = c.p / c.rho;
         c.a = sqrt(fmax(P.gamma * c.p / c.rho, P.eps));
     } else {
-        const double inv = __drcp_rn(c.rho);
+        const double inv = rcp_fast(c.rho);
         c.u = clipd((double)q.y * inv, -P.mv, P.mv);
         c.v = clipd((double)q.z * inv, -P.mv, P.mv);
         c.E = clipd((double)q.w * inv, P.eps, P.mv);
         c.p = fmax(P.gm1 * c.rho * (c.E - 0.5 * (c.u * c.u + c.v * c.v)), P.eps);
         pr = c.p * inv;
-        c.a = sqrt(fmax(P.gamma * pr, P.eps));
+        c.a = sqrt_fast(fmax(P.gamma * pr, P.eps));
     }
     const double H = c.E + pr, ru = c.rho * c.u, rv = c.rho * c.v;
     c.Fp = make_float4((float)ru, (float)(ru * c.u + c.p), (float)(ru * c.v), (float)(ru * H));
@@ -56,7 +78,7 @@ __device__ __forceinline__ Cell make_cell(const float4 q, const Phys& P) {
 __device__ __forceinline__ float4 f4zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 
 // hllc_solver (v1_shock.py:147-209). XN: normal (1,0), else (0,1).
-template <bool XN>
+template <bool XN, bool EXACT>
 __device__ __forceinline__ float4 hllc_face(const Cell& L, const Cell& R, const Phys& P) {
     if (L.rho <= P.eps || R.rho <= P.eps) return f4zero();                         // :152-153,160-161
     const double qL = XN ? L.u : L.v, qR = XN ? R.u : R.v;
@@ -65,18 +87,18 @@ __device__ __forceinline__ float4 hllc_face(const Cell& L, const Cell& R, const 
     if (SL >= 0) return fL;                                                         // :186-187
     if (SR <= 0) return fR;                                                         // :188-189
     const double mL = L.rho * (SL - qL), mR = R.rho * (SR - qR);
-    const double SM = (R.rho * qR * (SR - qR) - L.rho * qL * (SL - qL) + L.p - R.p) / (mR - mL + P.eps);   // :174
+    const double SM = dv<EXACT>(R.rho * qR * (SR - qR) - L.rho * qL * (SL - qL) + L.p - R.p, mR - mL + P.eps);   // :174
     const double pstar = L.rho * (qL - SL) * (qL - SM) + L.p;                       // :191
     // one star state, chosen by the sign of S_M (:199-209); selecting operands keeps the warp converged
     const bool left = SM >= 0;
     const double S = left ? SL : SR, m = left ? mL : mR, q = left ? qL : qR, p = left ? L.p : R.p;
     const double E = left ? L.E : R.E, vt = left ? L.v : R.v;
     const float4 f = left ? fL : fR, U = left ? L.U : R.U;
-    const double c = m / (S - SM + P.eps);
+    const double c = dv<EXACT>(m, S - SM + P.eps);
     const float s0 = (float)c;
     const float s1 = (float)(c * (XN ? SM : 0.0 * SM));
     const float s2 = (float)(c * (XN ? vt : SM));
-    const float s3 = (float)(c * (E + (pstar * SM - p * q) / (m + P.eps)));
+    const float s3 = (float)(c * (E + dv<EXACT>(pstar * SM - p * q, m + P.eps)));
     return make_float4((float)((double)f.x + S * (double)(s0 - U.x)), (float)((double)f.y + S * (double)(s1 - U.y)),
                        (float)((double)f.z + S * (double)(s2 - U.z)), (float)((double)f.w + S * (double)(s3 - U.w)));
 }
@@ -101,9 +123,9 @@ __device__ __forceinline__ float4 roe_face(const Cell& L, const Cell& R, const P
     return o;
 }
 
-template <int SOLVER, bool XN>
+template <int SOLVER, bool XN, bool EXACT = true>
 __device__ __forceinline__ float4 face_flux(const Cell& L, const Cell& R, const Phys& P) {
-    return SOLVER == 0 ? hllc_face<XN>(L, R, P) : roe_face<XN>(L, R, P);
+    return SOLVER == 0 ? hllc_face<XN, EXACT>(L, R, P) : roe_face<XN>(L, R, P);
 }
 
 // update_state (v1_shock.py:215-221) for one interior cell: west/east x-faces, south/north y-faces.
@@ -121,13 +143,28 @@ __device__ __forceinline__ float4 update_cell(const float4 U, const float4 Fw, c
 }
 
 // compute_dt's per-cell wave speeds (v1_shock.py:265-272): f32 NumPy divisions, then f64.
+// EXACT = false: one fast float64 reciprocal serves all four divisions.  The three float32 quotients keep their float32
+// rounding (they are the reference's np.float32 divisions; dropping it moved dt by up to 2e-6 in the parity runs): a
+// float64 quotient rounded to float32 is the float32 quotient, except where the 1-2 ulp of rcp_fast straddle a float32
+// rounding boundary (about one quotient in 2^28).
+template <bool EXACT = true>
 __device__ __forceinline__ void cell_speeds(const float4 q, const Phys& P, double& sx, double& sy) {
     const float rho = fmaxf(q.x, P.epsf);
-    const double u = clipd((double)__fdiv_rn(q.y, rho), -P.mv, P.mv);
-    const double v = clipd((double)__fdiv_rn(q.z, rho), -P.mv, P.mv);
-    const double E = clipd((double)__fdiv_rn(q.w, rho), P.eps, P.mv);
-    const double p = fmax((double)__fmul_rn(P.gm1f, rho) * (E - 0.5 * (u * u + v * v)), P.eps);
-    const double a = sqrt(clipd(P.gamma * p / (double)rho, P.eps, P.mv));
+    double u, v, E, a;
+    if (EXACT) {
+        u = clipd((double)__fdiv_rn(q.y, rho), -P.mv, P.mv);
+        v = clipd((double)__fdiv_rn(q.z, rho), -P.mv, P.mv);
+        E = clipd((double)__fdiv_rn(q.w, rho), P.eps, P.mv);
+        const double p = fmax((double)__fmul_rn(P.gm1f, rho) * (E - 0.5 * (u * u + v * v)), P.eps);
+        a = sqrt(clipd(P.gamma * p / (double)rho, P.eps, P.mv));
+    } else {
+        const double inv = rcp_fast((double)rho);
+        u = clipd((double)(float)((double)q.y * inv), -P.mv, P.mv);
+        v = clipd((double)(float)((double)q.z * inv), -P.mv, P.mv);
+        E = clipd((double)(float)((double)q.w * inv), P.eps, P.mv);
+        const double p = fmax((double)__fmul_rn(P.gm1f, rho) * (E - 0.5 * (u * u + v * v)), P.eps);
+        a = sqrt_fast(clipd(P.gamma * p * inv, P.eps, P.mv));
+    }
     sx = fabs(u) + a;
     sy = fabs(v) + a;
 }

@@ -209,6 +209,15 @@ static inline int pick_rpb(int bx, int ny, int slots, int halo_rows, int fallbac
     return best;
 }
 
+// The halo-lane kernels stop halving at 16 rows per block.  Where that still leaves fewer than 8 blocks per SM (4096x1024:
+// 1152 blocks, 2.6 waves of the finalize kernel) 12-row blocks measured faster (tools/r02v.sh: finalize 59.8 -> 58.8 us,
+// K2+K3 51.5 -> 49.3 us; 8, 20, 24 and longer are slower): more, shorter blocks fill the last wave better than the
+// extra halo rows cost.  Not for grids so small that the latency rule below takes over.
+static inline int rpb_12(int bx, int ny, int n_sm, int rpb) {
+    if (rpb == 16 && (long long)bx * ((ny + 15) / 16) < 8ll * n_sm && (long long)bx * ((ny + 15) / 16) >= 2ll * n_sm) return 12;
+    return rpb;
+}
+
 static inline int rows_per_block(const Geom& g, int n_sm) {
     // enough blocks for ~8 blocks per SM, chunks of 8..64 rows (multiples of the flag tile height)
     const int bx = (g.nx + FCOLS - 1) / FCOLS;
@@ -216,6 +225,8 @@ static inline int rows_per_block(const Geom& g, int n_sm) {
     while (rpb > 8 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
+    static const int force = getenv("B200CFD_PRED_RPB") ? atoi(getenv("B200CFD_PRED_RPB")) : 0;   // developer knob
+    if (force > 0) return force;
     return pick_rpb(bx, g.ny, 5 * n_sm, 2, rpb);             // k_predictor_fast: 5 blocks per SM (launch bounds)
 }
 
@@ -685,9 +696,12 @@ static inline dim3 finalize_fast_grid(const Geom& g, int n_sm, int* rpb_out) {
     static const int rpb_min = getenv("B200CFD_FIN_RPB_MIN") ? atoi(getenv("B200CFD_FIN_RPB_MIN")) : 16;   // developer knob
     int rpb = 64;
     while (rpb > rpb_min && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    rpb = rpb_12(bx, g.ny, n_sm, rpb);
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     rpb = pick_rpb(bx, g.ny, 3 * n_sm, 3, rpb);              // k_finalize_fast: 3 blocks per SM
+    static const int force = getenv("B200CFD_FIN_RPB") ? atoi(getenv("B200CFD_FIN_RPB")) : 0;      // developer knob
+    if (force > 0) rpb = force;
     *rpb_out = rpb;
     return dim3(bx, (g.ny + rpb - 1) / rpb);
 }
@@ -1002,9 +1016,12 @@ void launch_div_rb1_correct_fast(int dtype, const Geom& g, const void* us, const
     const int bx = (g.nx + FB_OWN - 1) / FB_OWN;
     int rpb = 64;
     while (rpb > 16 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 8ll * n_sm) rpb >>= 1;
+    rpb = rpb_12(bx, g.ny, n_sm, rpb);
     // small grids (the shipped 600x180 case): the kernel is pure latency, so trade redundant halo rows for parallelism
     while (rpb > 4 && (long long)bx * ((g.ny + rpb - 1) / rpb) < 2ll * n_sm) rpb >>= 1;
     rpb = pick_rpb(bx, g.ny, 4 * n_sm, 4, rpb);              // k_div_rb1_correct_fast: 4 blocks per SM
+    static const int force = getenv("B200CFD_K23_RPB") ? atoi(getenv("B200CFD_K23_RPB")) : 0;      // developer knob
+    if (force > 0) rpb = force;
     const dim3 grid(bx, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
 #define DCF(T, DIV) launch_pdl(k_div_rb1_correct_fast<T, DIV>, grid, dim3(FBT), s, g, (const T*)us, (const T*)vs, mask, (T*)phi, (T*)div_out, (T*)ua, (T*)va, inv_dt, ctl, flags, ntx, rpb, lean_on)

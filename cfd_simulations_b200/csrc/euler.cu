@@ -26,6 +26,12 @@
 
 namespace b200cfd { namespace eu {
 
+#ifndef EU_UNROLL2
+#define EU_UNROLL2 0                // 1: march unrolled by two rows (Cell variables swap roles instead of being copied): 138 registers instead of 124, measured slower (41.1 vs 43.4 Gcell/s)
+#endif
+#ifndef EU_PF
+#define EU_PF 6                     // L2 prefetch distance of the state rows (0 = off)
+#endif
 constexpr int WARPS = 4;            // warps per block (independent: no barrier in the step kernel)
 constexpr int OUT_LANES = 30;       // written columns per warp window
 constexpr int RING = 1 << 16;
@@ -56,28 +62,30 @@ struct StepParams {
 struct Acc { double sx, sy; unsigned nan; };
 
 template <bool EXACT>
-__device__ __forceinline__ void put(float4* __restrict__ out, const uint8_t* __restrict__ wedge, size_t idx, float4 q,
+__device__ __forceinline__ void put(float4* __restrict__ out, const unsigned wedge_byte, size_t idx, float4 q,
                                     const Phys& P, Acc& acc) {
-    if (wedge[idx]) { q.y = 0.f; q.z = 0.f; }                       // :312-313
+    if (wedge_byte) { q.y = 0.f; q.z = 0.f; }                       // :312-313
     out[idx] = q;
     double sx, sy;
     cell_speeds<EXACT>(q, P, sx, sy);
     acc.nan |= (q.x != q.x) | (q.y != q.y) | (q.z != q.z) | (q.w != q.w) | (sx != sx) | (sy != sy);
-    acc.sx = fmax(acc.sx, sx);
-    acc.sy = fmax(acc.sy, sy);
+    acc.sx = vmax<EXACT>(sx, acc.sx);        // a NaN speed never wins (it is flagged above)
+    acc.sy = vmax<EXACT>(sy, acc.sy);
 }
 
 // One cell of row i after update_state, through the y-boundary part of apply_boundary_conditions (:284-289):
 // flip the reflective prefix, then (if any column is not reflective) copy into the two border columns.
+// wb: the wedge-mask byte of cell (i, c), loaded by the caller ahead of the arithmetic (a load issued here, right before
+// its use, left a full global-load latency exposed on every row: 21 % of the kernel's stall samples).
 template <bool EXACT>
 __device__ __forceinline__ void emit(float4* __restrict__ out, const uint8_t* __restrict__ wedge, const StepParams& S,
-                                     int i, int c, float4 q, Acc& acc) {
+                                     int i, int c, float4 q, Acc& acc, const unsigned wb) {
     if (c < S.n_reflect) q.z = -q.z;
     const size_t row = (size_t)i * S.ny;
-    put<EXACT>(out, wedge, row + c, q, S.phys, acc);
+    put<EXACT>(out, wb, row + c, q, S.phys, acc);
     if (S.n_reflect < S.ny) {
-        if (c == 1) put<EXACT>(out, wedge, row, q, S.phys, acc);
-        if (c == S.ny - 2) put<EXACT>(out, wedge, row + S.ny - 1, q, S.phys, acc);
+        if (c == 1) put<EXACT>(out, wedge[row], row, q, S.phys, acc);
+        if (c == S.ny - 2) put<EXACT>(out, wedge[row + S.ny - 1], row + S.ny - 1, q, S.phys, acc);
     }
 }
 
@@ -115,7 +123,7 @@ k_euler_step(const StepParams S, const float4* __restrict__ in, float4* __restri
     const double ax = dt / S.dx, ay = dt / S.dy;
     Acc acc = {0.0, 0.0, 0u};
 
-    if (writes && chunk == 0 && S.inflow_row >= 0) emit<EXACT>(out, wedge, S, S.inflow_row, c, S.fs, acc);   // :279-282
+    if (writes && chunk == 0 && S.inflow_row >= 0) emit<EXACT>(out, wedge, S, S.inflow_row, c, S.fs, acc, wedge[(size_t)S.inflow_row * S.ny + c]);   // :279-282
 
     const float4* col = in + cc;
     float4 qN = __ldg(col + (size_t)(r0 + 1) * S.ny);
@@ -125,22 +133,38 @@ k_euler_step(const StepParams S, const float4* __restrict__ in, float4* __restri
         const Cell W = make_cell<EXACT>(__ldg(col + (size_t)(r0 - 1) * S.ny), P);
         Fw = face_flux<SOLVER, true, EXACT>(W, C, P);
     }
-    for (int i = r0; i <= r1; ++i) {
+    const uint8_t* wcol = wedge + cc;
+    unsigned wbN = __ldg(wcol + (size_t)r0 * S.ny);
+    // one row: Cc = cell (i, c), Nn receives cell (i+1, c).  Called with the two Cell variables swapped on alternate rows, so
+    // that the 24 registers of a Cell are renamed instead of copied.
+    auto row = [&](const int i, const Cell& Cc, Cell& Nn) {
         const float4 qNN = __ldg(col + (size_t)min(i + 2, S.nx - 1) * S.ny);   // next iteration's row, in flight during the math
-        const Cell N = make_cell<EXACT>(qN, P);
-        const float4 Fe = face_flux<SOLVER, true, EXACT>(C, N, P);                     // x-face (i | i+1)
-        const Cell Y = shfl_down_cell<SOLVER>(C);                               // cell (i, c+1)
-        const float4 Gn = face_flux<SOLVER, false, EXACT>(C, Y, P);                    // y-face (c | c+1)
+        if (EU_PF > 0 && i + EU_PF < S.nx) asm volatile("prefetch.global.L2 [%0];" ::"l"(col + (size_t)(i + EU_PF) * S.ny));
+        const unsigned wb = wbN;                                               // wedge bytes: this row's arrived, next row's requested
+        wbN = __ldg(wcol + (size_t)min(i + 1, S.nx - 1) * S.ny);
+        unsigned wbO = 0;
+        if (i + 1 == S.outflow_row) wbO = __ldg(wcol + (size_t)S.outflow_row * S.ny);
+        Nn = make_cell<EXACT>(qN, P);
+        const float4 Fe = face_flux<SOLVER, true, EXACT>(Cc, Nn, P);            // x-face (i | i+1)
+        const Cell Y = shfl_down_cell<SOLVER>(Cc);                              // cell (i, c+1)
+        const float4 Gn = face_flux<SOLVER, false, EXACT>(Cc, Y, P);            // y-face (c | c+1)
         const float4 Gs = shfl_up4(Gn);                                         // y-face (c-1 | c)
         if (writes) {
-            const float4 q = update_cell(C.U, Fw, Fe, Gs, Gn, ax, ay, P);
-            emit<EXACT>(out, wedge, S, i, c, q, acc);
-            if (i + 1 == S.outflow_row) emit<EXACT>(out, wedge, S, S.outflow_row, c, q, acc);            // :283
+            const float4 q = update_cell<EXACT>(Cc.U, Fw, Fe, Gs, Gn, ax, ay, P);
+            emit<EXACT>(out, wedge, S, i, c, q, acc, wb);
+            if (i + 1 == S.outflow_row) emit<EXACT>(out, wedge, S, S.outflow_row, c, q, acc, wbO);       // :283
         }
         Fw = Fe;
-        C = N;
         qN = qNN;
-    }
+    };
+    Cell D;
+    int i = r0;
+#if EU_UNROLL2
+    for (; i + 1 <= r1; i += 2) { row(i, C, D); row(i + 1, D, C); }
+    if (i <= r1) row(i, C, D);
+#else
+    for (; i <= r1; ++i) { row(i, C, D); C = D; }
+#endif
     // block-free reduction: warp shuffle, one atomic per warp and quantity
     double sx = acc.sx, sy = acc.sy;
     unsigned nan = acc.nan;

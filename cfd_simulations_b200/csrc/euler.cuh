@@ -44,30 +44,45 @@ __device__ __forceinline__ double sqrt_fast(double x) {      // x > 0
     y = y * fma(-(hx * y), y, 1.5);
     return x * y;
 }
+// x rounded to 24 significant bits (what a conversion to float32 and back gives for numbers in float32's normal range) with
+// three fp64-pipe operations (Veltkamp splitting) instead of two conversions: the conversion pipe (XU, a quarter of the
+// fp64 rate) is this kernel's busiest.
+__device__ __forceinline__ double rnd24(double x) {
+    const double t = __dmul_rn(x, 536870913.0);          // 2^29 + 1
+    return __dsub_rn(t, __dsub_rn(t, x));
+}
 template <bool EXACT> __device__ __forceinline__ double dv(double a, double b) { return EXACT ? a / b : a * rcp_fast(b); }
+// fmax / fmin / clip.  The library forms quiet and drop NaNs the IEEE way, which costs 7-8 instructions each on sm_100a
+// (DSETP.MAX, two selects, a NaN fix-up and the moves around them) and there are about thirty per cell; the default mode
+// uses a compare and a select (3 instructions).  Same result for ordinary numbers and when the FIRST argument is NaN (the
+// second is returned); a NaN in the second argument is returned instead of dropped — a state with NaNs is reported
+// through the nan flag either way.
+template <bool EXACT> __device__ __forceinline__ double vmax(double a, double b) { return EXACT ? fmax(a, b) : (a > b ? a : b); }
+template <bool EXACT> __device__ __forceinline__ double vmin(double a, double b) { return EXACT ? fmin(a, b) : (a < b ? a : b); }
+template <bool EXACT> __device__ __forceinline__ double vclip(double x, double lo, double hi) { return vmax<EXACT>(vmin<EXACT>(x, hi), lo); }
 
 // EXACT: IEEE divisions where the reference divides (bit-faithful); otherwise one reciprocal per cell.
 template <bool EXACT>
 __device__ __forceinline__ Cell make_cell(const float4 q, const Phys& P) {
     Cell c;
     c.U = q;
-    c.rho = fmax((double)q.x, P.eps);
+    c.rho = vmax<EXACT>((double)q.x, P.eps);
     double pr;
     if (EXACT) {
-        c.u = clipd((double)q.y / c.rho, -P.mv, P.mv);
-        c.v = clipd((double)q.z / c.rho, -P.mv, P.mv);
-        c.E = clipd((double)q.w / c.rho, P.eps, P.mv);
-        c.p = fmax(P.gm1 * c.rho * (c.E - 0.5 * (c.u * c.u + c.v * c.v)), P.eps);
+        c.u = vclip<EXACT>((double)q.y / c.rho, -P.mv, P.mv);
+        c.v = vclip<EXACT>((double)q.z / c.rho, -P.mv, P.mv);
+        c.E = vclip<EXACT>((double)q.w / c.rho, P.eps, P.mv);
+        c.p = vmax<EXACT>(P.gm1 * c.rho * (c.E - 0.5 * (c.u * c.u + c.v * c.v)), P.eps);
         pr = c.p / c.rho;
-        c.a = sqrt(fmax(P.gamma * c.p / c.rho, P.eps));
+        c.a = sqrt(vmax<EXACT>(P.gamma * c.p / c.rho, P.eps));
     } else {
         const double inv = rcp_fast(c.rho);
-        c.u = clipd((double)q.y * inv, -P.mv, P.mv);
-        c.v = clipd((double)q.z * inv, -P.mv, P.mv);
-        c.E = clipd((double)q.w * inv, P.eps, P.mv);
-        c.p = fmax(P.gm1 * c.rho * (c.E - 0.5 * (c.u * c.u + c.v * c.v)), P.eps);
+        c.u = vclip<EXACT>((double)q.y * inv, -P.mv, P.mv);
+        c.v = vclip<EXACT>((double)q.z * inv, -P.mv, P.mv);
+        c.E = vclip<EXACT>((double)q.w * inv, P.eps, P.mv);
+        c.p = vmax<EXACT>(P.gm1 * c.rho * (c.E - 0.5 * (c.u * c.u + c.v * c.v)), P.eps);
         pr = c.p * inv;
-        c.a = sqrt_fast(fmax(P.gamma * pr, P.eps));
+        c.a = sqrt_fast(vmax<EXACT>(P.gamma * pr, P.eps));
     }
     const double H = c.E + pr, ru = c.rho * c.u, rv = c.rho * c.v;
     c.Fp = make_float4((float)ru, (float)(ru * c.u + c.p), (float)(ru * c.v), (float)(ru * H));
@@ -82,7 +97,7 @@ template <bool XN, bool EXACT>
 __device__ __forceinline__ float4 hllc_face(const Cell& L, const Cell& R, const Phys& P) {
     if (L.rho <= P.eps || R.rho <= P.eps) return f4zero();                         // :152-153,160-161
     const double qL = XN ? L.u : L.v, qR = XN ? R.u : R.v;
-    const double SL = fmin(qL - L.a, qR - R.a), SR = fmax(qL + L.a, qR + R.a);      // :172-173
+    const double SL = vmin<EXACT>(qL - L.a, qR - R.a), SR = vmax<EXACT>(qL + L.a, qR + R.a);      // :172-173
     const float4 fL = XN ? L.Fp : L.Gp, fR = XN ? R.Fp : R.Gp;
     if (SL >= 0) return fL;                                                         // :186-187
     if (SR <= 0) return fR;                                                         // :188-189
@@ -129,16 +144,17 @@ __device__ __forceinline__ float4 face_flux(const Cell& L, const Cell& R, const 
 }
 
 // update_state (v1_shock.py:215-221) for one interior cell: west/east x-faces, south/north y-faces.
+template <bool EXACT = true>
 __device__ __forceinline__ float4 update_cell(const float4 U, const float4 Fw, const float4 Fe, const float4 Gs, const float4 Gn,
                                               double ax, double ay, const Phys& P) {
     double r = (double)U.x - ax * (double)(Fe.x - Fw.x) - ay * (double)(Gn.x - Gs.x);
     double mx = (double)U.y - ax * (double)(Fe.y - Fw.y) - ay * (double)(Gn.y - Gs.y);
     double my = (double)U.z - ax * (double)(Fe.z - Fw.z) - ay * (double)(Gn.z - Gs.z);
     double e = (double)U.w - ax * (double)(Fe.w - Fw.w) - ay * (double)(Gn.w - Gs.w);
-    r = fmax(r, P.eps);
-    mx = clipd(mx, -P.mv * r, P.mv * r);
-    my = clipd(my, -P.mv * r, P.mv * r);
-    e = fmax(e, P.eps * r);
+    r = vmax<EXACT>(r, P.eps);
+    mx = vclip<EXACT>(mx, -P.mv * r, P.mv * r);
+    my = vclip<EXACT>(my, -P.mv * r, P.mv * r);
+    e = vmax<EXACT>(e, P.eps * r);
     return make_float4((float)r, (float)mx, (float)my, (float)e);
 }
 
@@ -159,11 +175,11 @@ __device__ __forceinline__ void cell_speeds(const float4 q, const Phys& P, doubl
         a = sqrt(clipd(P.gamma * p / (double)rho, P.eps, P.mv));
     } else {
         const double inv = rcp_fast((double)rho);
-        u = clipd((double)(float)((double)q.y * inv), -P.mv, P.mv);
-        v = clipd((double)(float)((double)q.z * inv), -P.mv, P.mv);
-        E = clipd((double)(float)((double)q.w * inv), P.eps, P.mv);
-        const double p = fmax((double)__fmul_rn(P.gm1f, rho) * (E - 0.5 * (u * u + v * v)), P.eps);
-        a = sqrt_fast(clipd(P.gamma * p * inv, P.eps, P.mv));
+        u = vclip<false>(rnd24((double)q.y * inv), -P.mv, P.mv);
+        v = vclip<false>(rnd24((double)q.z * inv), -P.mv, P.mv);
+        E = vclip<false>(rnd24((double)q.w * inv), P.eps, P.mv);
+        const double p = vmax<false>((double)__fmul_rn(P.gm1f, rho) * (E - 0.5 * (u * u + v * v)), P.eps);
+        a = sqrt_fast(vclip<false>(P.gamma * p * inv, P.eps, P.mv));
     }
     sx = fabs(u) + a;
     sy = fabs(v) + a;

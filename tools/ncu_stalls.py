@@ -10,7 +10,7 @@ import sys
 src, dst = sys.argv[1], sys.argv[2]
 out = subprocess.run(["ncu", "-i", src, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-kern, hdr, agg, hot, seen = None, None, {}, {}, set()
+kern, hdr, agg, hot, seen, seq = None, None, {}, {}, set(), {}
 for r in rows:
     if r and r[0] == "Kernel Name":
         kern = r[1][:90]
@@ -33,6 +33,7 @@ for r in rows:
     op = toks[1] if toks and toks[0].startswith("@") and len(toks) > 1 else (toks[0] if toks else "?")
     agg[kern][op.split(".")[0]] += n
     hot[kern].append((n, r[1].strip()[:80]))
+    seq.setdefault(kern, []).append(r[1].strip()[:80])
 with open(dst, "w") as f:
     f.write(f"# warp-stall samples by opcode: {src}\n")
     for k, c in agg.items():
@@ -41,3 +42,9 @@ with open(dst, "w") as f:
         f.write(" ".join(f"{op} {100 * n / tot:.1f}%" for op, n in c.most_common(12)) + "\n\nhottest lines:\n\n")
         for n, line in sorted(hot[k], reverse=True)[:10]:
             f.write(f"    {100 * n / tot:5.1f}%  {line}\n")
+        # the twelve instructions in front of the two hottest lines (what they wait for)
+        for n, line in sorted(hot[k], reverse=True)[:2]:
+            i = seq[k].index(line)
+            f.write(f"\ncontext of `{line}`:\n\n")
+            for l in seq[k][max(0, i - 12):i + 2]:
+                f.write(f"    {l}\n")

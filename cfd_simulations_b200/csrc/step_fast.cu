@@ -123,16 +123,66 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
 }
 
 
+// The lean rows of k_predictor_fast: every column of the block is an interior column with both x-neighbours, no flag tile
+// over the block carries ibm > 0, rows [lo - 1, hi] exist and hi - lo is a multiple of 4.  Then BC, IBM and the column
+// classes drop out and what is left is written for the issue slots (the general loop: 437 instructions per lane-row, 151
+// of them fp64 arithmetic): rows rotate through register arrays indexed by (row & 3) in a loop unrolled by 4, and eight
+// lanes of a warp prefetch the eight 128-byte lines of the row FPF ahead instead of all 32 lanes prefetching twice.
+// predict_fast() is the same function the general rows call, so a cell gets the same bits on either path.
+template <typename T, bool TAU>
+__device__ __forceinline__ void predictor_rows_lean(const Geom& g, const Phys& p, const double dt, const T* __restrict__ u,
+                                                    const T* __restrict__ v, T* __restrict__ us, T* __restrict__ vs,
+                                                    T* __restrict__ tau_out, const int lo, const int hi, const int j0) {
+    const double half_h = 0.5 * g.hmin, tau_cap = 0.25 * g.hmin * g.hmin / (p.nu_eff + 1e-10);
+    const long long pitch = g.pitch;
+    long long k = (long long)lo * pitch + j0;
+    D2 U[4], V[4];                                    // rows i-1, i, i+1 and the row in flight: slot (row - lo + 1) & 3
+    double UW[2], UE[2], VW[2], VE[2];                // x-neighbours of the lane's column pair: slot (row - lo) & 1
+    U[0] = ld2<T>(u, k - pitch); V[0] = ld2<T>(v, k - pitch);
+    U[1] = ld2<T>(u, k); V[1] = ld2<T>(v, k);
+    U[2] = ld2<T>(u, k + pitch); V[2] = ld2<T>(v, k + pitch);
+    UW[0] = ld(u, k - 1); UE[0] = ld(u, k + 2); VW[0] = ld(v, k - 1); VE[0] = ld(v, k + 2);
+    const int lane = threadIdx.x & 31;
+    const T* pf = (lane < 4 ? u : v) + (long long)(lo + FPF) * pitch + (j0 - 2 * lane) + (lane & 3) * (int)(128 / sizeof(T));
+    for (int i4 = lo; i4 < hi; i4 += 4) {
+        const bool more = i4 + 4 < hi;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (r < 3 || more) {                      // row i+2, and the x-neighbours of row i+1
+                U[(r + 3) & 3] = ld2<T>(u, k + 2 * pitch); V[(r + 3) & 3] = ld2<T>(v, k + 2 * pitch);
+                UW[(r + 1) & 1] = ld(u, k + pitch - 1); UE[(r + 1) & 1] = ld(u, k + pitch + 2);
+                VW[(r + 1) & 1] = ld(v, k + pitch - 1); VE[(r + 1) & 1] = ld(v, k + pitch + 2);
+            }
+            if (lane < 8 && i4 + r + FPF < g.ny) pf_l2(pf);
+            pf += pitch;
+            const D2 um = U[r], uc = U[(r + 1) & 3], un = U[(r + 2) & 3], vm = V[r], vc = V[(r + 1) & 3], vn = V[(r + 2) & 3];
+            double ru0, rv0, t0, ru1, rv1, t1;
+            predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.x, uc.y, UW[r & 1], un.x, um.x, vc.x, vc.y, VW[r & 1], vn.x, vm.x, ru0, rv0, t0);
+            predict_fast<T>(g, p.nu_eff, half_h, tau_cap, dt, uc.y, UE[r & 1], uc.x, un.y, um.y, vc.y, VE[r & 1], vc.x, vn.y, vm.y, ru1, rv1, t1);
+            st2<T>(us, k, ru0, ru1);
+            st2<T>(vs, k, rv0, rv1);
+            if (TAU) st2<T>(tau_out, k, t0, t1);
+            k += pitch;
+        }
+    }
+}
+
 template <typename T, bool TAU>
 __global__ void __launch_bounds__(FBT, 5)
 k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
                  T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const double* __restrict__ ibm,
-                 const double* __restrict__ y, const uint8_t* __restrict__ flags, int ntx, int rpb) {
+                 const double* __restrict__ y, const uint8_t* __restrict__ flags, int ntx, int rpb, int lean_on) {
     pdl_wait(); pdl_trigger();
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int cb = blockIdx.x * FCOLS;
     const int j0 = cb + 2 * threadIdx.x;
     const bool has_ibm = block_tile_flagged(flags, ntx, cb, min(cb + FCOLS, g.nx), r0, r1, 1);
+    // lean rows (see predictor_rows_lean): a block-uniform choice
+    if (lean_on && !has_ibm && r0 >= 1 && r1 <= g.ny - 1 && ((r1 - r0) & 3) == 0 &&
+        __syncthreads_and(j0 >= 1 && j0 + 2 < g.nx && col_class(g, j0) == COL_INTERIOR && col_class(g, j0 + 1) == COL_INTERIOR)) {
+        predictor_rows_lean<T, TAU>(g, p, ctl->dt, u, v, us, vs, tau_out, r0, r1, j0);
+        return;
+    }
     if (j0 >= g.nx) return;
     const int cx = col_class(g, j0), cy = col_class(g, j0 + 1);
     const bool hw = j0 >= 1, he = j0 + 2 < g.nx;             // west / east neighbour columns exist
@@ -243,7 +293,8 @@ void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCt
     const int rpb = rows_per_block(g, n_sm);
     const dim3 grid((g.nx + FCOLS - 1) / FCOLS, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define PF(T, TAU) launch_pdl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb)
+#define PF(T, TAU) launch_pdl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb, lean_on)
+    static const int lean_on = getenv("B200CFD_PRED_LEAN") ? atoi(getenv("B200CFD_PRED_LEAN")) : 1;   // developer knob (A/B)
     if (dtype == 0) { if (tau) PF(double, true); else PF(double, false); }
     else { if (tau) PF(float, true); else PF(float, false); }
 #undef PF

@@ -10,6 +10,7 @@ python bench.py --impl reference --steps 3 --warmup 1 > $o/${tag}_bench_ref.log 
 python bench_poisson.py --depths 1,0 > $o/${tag}_poisson.log 2>&1; echo "poisson rc=$?"
 python bench_euler.py > $o/${tag}_euler.log 2>&1; echo "euler rc=$?"
 bash tools/phases.sh > $o/${tag}_phases.txt 2>&1; cat $o/${tag}_phases.txt
+python tools/f32_speed.py 16384 8192 20 > $o/${tag}_f32_speed.txt 2>&1; python tools/f32_speed.py 4096 1024 50 >> $o/${tag}_f32_speed.txt 2>&1; python tools/f32_speed.py 600 180 200 >> $o/${tag}_f32_speed.txt 2>&1; grep ratio $o/${tag}_f32_speed.txt
 # ---- ncu: launch list + full captures (each command ran plain right before)
 P="python bench.py --steps 3 --warmup 3 --no-cpu --no-scaling-base --no-poisson"
 $P > $o/plain_step.log 2>&1 && timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv $P > $o/ncu_list.log 2>&1; echo "ncu list rc=$?"
@@ -25,15 +26,18 @@ timeout 600 ncu --set full --clock-control none -k regex:"k_(jacobi|rbgs_color)"
 QT="env B200CFD_POISSON_STREAM=0 python bench_poisson.py --no-cpu --sweeps 24 --depths 0"
 $QT > $o/plain_poisson_tile.log 2>&1 && timeout 600 ncu --set full --clock-control none -k regex:"k_(poisson_tb|tb_make_rhs)" --launch-skip 2 --launch-count 6 -f -o $o/prof_${tag}_poisson_tile $QT > $o/ncu_pt.log 2>&1; echo "ncu poisson tile rc=$?"
 E="python bench_euler.py --steps 3 --warmup 3 --no-cpu"
-$E > $o/plain_euler.log 2>&1 && timeout 600 ncu --set full --clock-control none -k regex:"k_euler" --launch-skip 4 --launch-count 3 -f -o $o/prof_${tag}_euler $E > $o/ncu_e.log 2>&1; echo "ncu euler rc=$?"
+$E > $o/plain_euler.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_euler" --launch-skip 4 --launch-count 3 -f -o $o/prof_${tag}_euler $E > $o/ncu_e.log 2>&1; echo "ncu euler rc=$?"
 H="python tools/slab_case.py"
 $H > $o/plain_slab.log 2>&1 && timeout 600 ncu --set full --clock-control none -k regex:"k_(halo_rows|columns|sor_v2_bc)" --launch-count 6 -f -o $o/prof_${tag}_halo $H > $o/ncu_h.log 2>&1; echo "ncu halo rc=$?"
 # ---- summarise on the box and drop the reports (gpurun_out/ comes back only if it stays under 64 MiB)
 for r in step step16384 poisson_stream poisson_1sweep poisson_tile euler halo; do
   [ -f $o/prof_${tag}_$r.ncu-rep ] && python tools/ncu_summary.py full $o/prof_${tag}_$r.ncu-rep $o/${tag}_${r}_full.md $o/${tag}_traffic_$r.json
 done
-for r in step poisson_stream; do
+for r in step poisson_stream euler; do
   [ -f $o/prof_${tag}_$r.ncu-rep ] && python tools/ncu_stalls.py $o/prof_${tag}_$r.ncu-rep $o/${tag}_${r}_stalls.md
+done
+for r in step step16384 poisson_stream euler; do
+  [ -f $o/prof_${tag}_$r.ncu-rep ] && python tools/ncu_warpstate.py $o/prof_${tag}_$r.ncu-rep $o/${tag}_${r}_warpstate.md
 done
 rm -f $o/*.ncu-rep
 du -sh $o

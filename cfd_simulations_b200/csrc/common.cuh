@@ -101,8 +101,13 @@ template <> __device__ __forceinline__ double axpy_pred<float>(double a, double 
 }
 // a - s*g evaluated in the field dtype (v5.py:416-417)
 template <typename T> __device__ __forceinline__ double axmy(double a, double s, double g);
-template <> __device__ __forceinline__ double axmy<double>(double a, double s, double g) { return a - s * g; }
-template <> __device__ __forceinline__ double axmy<float>(double a, double s, double g) { return (double)((float)a - (float)s * (float)g); }
+// Written with explicit intrinsics: two roundings, as NumPy evaluates `u_star - dt * grad`.  Left as `a - s * g` the compiler
+// is free to contract it into one FMA or not, and it chose differently in the lean and in the general rows of K2+K3
+// (tests/test_gpu_lean_paths.py found 3 cells of 786 432 one ulp apart after 5 steps).
+template <> __device__ __forceinline__ double axmy<double>(double a, double s, double g) { return __dsub_rn(a, __dmul_rn(s, g)); }
+template <> __device__ __forceinline__ double axmy<float>(double a, double s, double g) {
+    return (double)__fsub_rn((float)a, __fmul_rn((float)s, (float)g));
+}
 
 __device__ __forceinline__ double warp_max(double v) {
 #pragma unroll

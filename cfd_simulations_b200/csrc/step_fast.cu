@@ -128,7 +128,7 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
 // classes drop out and what is left is written for the issue slots (the general loop: 437 instructions per lane-row, 151
 // of them fp64 arithmetic): rows rotate through register arrays indexed by (row & 3) in a loop unrolled by 4, and eight
 // lanes of a warp prefetch the eight 128-byte lines of the row FPF ahead instead of all 32 lanes prefetching twice.
-// predict_fast() is the same function the general rows call, so a cell gets the same bits on either path.
+// predict_fast() is the same function the general rows call, and the two paths agree bit for bit in tests/test_gpu_lean_paths.py.
 template <typename T, bool TAU>
 __device__ __forceinline__ void predictor_rows_lean(const Geom& g, const Phys& p, const double dt, const T* __restrict__ u,
                                                     const T* __restrict__ v, T* __restrict__ us, T* __restrict__ vs,
@@ -439,8 +439,8 @@ __device__ __forceinline__ void max_abs(double& acc, double x) { const double a 
 //   * clip / NaN bookkeeping (v5.py:431-438) is one warp vote per row: only a row that holds a value outside
 //     [-vmax, vmax] or a NaN takes the exact per-cell code;
 //   * one prefetch instruction per row covers the four input arrays (lane -> array, 128-byte line).
-// Same operations in the same order per cell as the general rows (shared helpers), so a cell gets the same bits whichever
-// path its warp takes.
+// Same operations in the same order per cell as the general rows (shared helpers); the two paths agree bit for bit in
+// tests/test_gpu_lean_paths.py.
 template <typename T, int NPSI>
 __device__ __forceinline__ void finalize_rows_lean(const Geom& g, const double vmax, const T* __restrict__ ua, const T* __restrict__ va,
                                                    const T* __restrict__ psi, const T* __restrict__ psi1, T* __restrict__ u,
@@ -806,7 +806,10 @@ void launch_finalize_fast(int dtype, const Geom& g, const Phys& p, StepCtl* ctl,
 //     neighbour of the even cells above and below (the general rows evaluate it three times);
 //   * the two halo lanes fetch their outer u* neighbour with one predicated load per row;
 //   * reductions run unweighted per lane, ownership is applied once after the loop.
-// Per cell the operations and their order are those of the general rows, so a cell gets the same bits on either path.
+// Per cell the operations and their order are those of the general rows.  The bits agree too, except that the redundant phi
+// row above a block is computed by the prologue's copy of the formula here and by the loop's in the general rows, and the
+// compiler contracts a*x + b*y - c into FMAs differently in the two: a handful of cells of v end up one ulp apart
+// (tests/test_gpu_lean_paths.py: 3 of 786 432 after 5 steps).
 __device__ __forceinline__ void max_pos(double& acc, double x) { acc = x > acc ? x : acc; }
 
 template <typename T, bool DIV>

@@ -55,8 +55,11 @@ class OptimizedTurbulentSolver:
     """
 
     def __init__(self, config, device=0, poisson_mode="as_executed", cleandiv_mode="lexicographic", omega=1.0,
-                 clean_iters=2, use_graph=True, nranks=1, rank=0, group=None, setup="host"):
-        """nranks > 1: this process holds x-slab `rank` of `nranks` (multigpu.py; torch.distributed must be
+                 clean_iters=2, use_graph=True, nranks=1, rank=0, group=None, setup="host", materialize_attributes=True):
+        """materialize_attributes=False: the two arrays the reference keeps only as by-products of a step, `tau_supg`
+        (v5.py:392) and `div_u_star` (v5.py:409), are not written (b200cfd_bind_fields takes NULL for them): 176 instead of
+        192 B/cell per step; u, v, phi, u_star, v_star and every logged scalar are unchanged, reading the two attributes raises.
+        nranks > 1: this process holds x-slab `rank` of `nranks` (multigpu.py; torch.distributed must be
         initialised, NCCL).  setup = "host" (NumPy, bit-identical to the reference's arrays) | "device" (torch on the
         GPU, for slabs too large for comfortable host setup; p is not allocated)."""
         if not torch.cuda.is_available():
@@ -105,9 +108,13 @@ class OptimizedTurbulentSolver:
         self._h = C.c_void_p()
         check(self._lib.b200cfd_create(C.byref(self._ccfg), device, C.byref(self._h)))
         d = self._d
+        self._attributes = bool(materialize_attributes)
+        if not self._attributes:
+            del d["div_u_star"], d["tau_supg"]
         check(self._lib.b200cfd_bind_fields(self._h, d["u"].data_ptr(), d["v"].data_ptr(), d["phi"].data_ptr(),
-                                            d["u_star"].data_ptr(), d["v_star"].data_ptr(), d["div_u_star"].data_ptr(),
-                                            d["tau_supg"].data_ptr(), d["nu_t"].data_ptr(), d["ibm"].data_ptr(),
+                                            d["u_star"].data_ptr(), d["v_star"].data_ptr(),
+                                            d["div_u_star"].data_ptr() if self._attributes else None,
+                                            d["tau_supg"].data_ptr() if self._attributes else None, d["nu_t"].data_ptr(), d["ibm"].data_ptr(),
                                             d["mask"].data_ptr(), d["y"].data_ptr()), self._h)
         self._step = 0
         self._fetched = 0            # scalars of steps [first_step, _fetched) are in self.scalars
@@ -148,6 +155,8 @@ class OptimizedTurbulentSolver:
 
     # ---- reference attributes: host views of device state (lazy D2H) ----
     def _get(self, name):
+        if name not in self._d:
+            raise B200CFDError(f"{name} is not materialised (materialize_attributes=False)")
         return self._d[name].cpu().numpy()
 
     def _set(self, name, value):

@@ -137,3 +137,23 @@ def test_snapshot_of_device_setup_solver(tmp_path):
     ok = ~np.isnan(wb)
     assert np.abs(s["vorticity"][ok] - wb[ok]).max() <= 1e-6 * np.abs(wb[ok]).max()   # device setup: transcendental ulps
     a.close(); b.close()
+
+
+def test_without_the_by_product_attributes_the_state_is_bit_identical():
+    """materialize_attributes=False: tau_supg / div_u_star are not written (NULL in b200cfd_bind_fields); everything else is
+    the same computation."""
+    from cfd_simulations_b200._lib import B200CFDError
+    from cfd_simulations_b200.config import OptimizedTurbulentConfig
+    from cfd_simulations_b200.solver import OptimizedTurbulentSolver
+    cfg = OptimizedTurbulentConfig(nx=768, ny=256, memory_efficient=False)
+    a = OptimizedTurbulentSolver(cfg, device=0)
+    b = OptimizedTurbulentSolver(cfg, device=0, materialize_attributes=False)
+    a.advance(15); b.advance(15)
+    for k in ("u", "v", "phi", "u_star", "v_star"):
+        assert np.array_equal(getattr(a, k), getattr(b, k)), k
+    assert [e for _, e in a.energy_history] == [e for _, e in b.energy_history]
+    with pytest.raises(B200CFDError):
+        b.tau_supg
+    with pytest.raises(B200CFDError):
+        b.div_u_star
+    a.close(); b.close()

@@ -318,39 +318,41 @@ def slab_poisson(slabs, rhs, max_iter, tol, omega, exchange, reduce_max):
     for s in slabs:                                           # the right-hand side does not change between the chunks
         s._lib.b200cfd_poisson_keep_rhs(s._h, 0)
     first = True
-    while it < max_iter:
-        m = min(T, max_iter - it)
-        if not first:
-            for s in slabs:
-                s._lib.b200cfd_poisson_keep_rhs(s._h, 1)
-        first = False
-        if check_tol:
-            for s, b in zip(slabs, backups):
-                b.copy_(s._d["phi"])
-        run(m, check_tol, final=(it + m >= max_iter))
-        g = None
-        stop = None
-        if check_tol:
-            g = reduce_max([c[:m] for c in chg]).tolist()     # one collective + one host read per chunk
-            last = g[m - 1]
-        elif it + m >= max_iter:                              # fixed count: only the final change is reported
-            last = float(reduce_max([v.clone() for v in views]).tolist()[0])
-        if check_tol:
-            for k, c in enumerate(g):
-                if c < tol:
-                    stop = k
-                    break
-        if stop is not None:
-            if stop + 1 < m:                                  # overshot: replay the chunk up to the stopping iteration
+    try:
+        while it < max_iter:
+            m = min(T, max_iter - it)
+            if not first:
+                for s in slabs:
+                    s._lib.b200cfd_poisson_keep_rhs(s._h, 1)
+            first = False
+            if check_tol:
                 for s, b in zip(slabs, backups):
-                    s._d["phi"].copy_(b)
-                run(stop + 1, False)
-            it += stop + 1
-            last = g[stop]
+                    b.copy_(s._d["phi"])
+            run(m, check_tol, final=(it + m >= max_iter))
+            g = None
+            stop = None
+            if check_tol:
+                g = reduce_max([c[:m] for c in chg]).tolist()     # one collective + one host read per chunk
+                last = g[m - 1]
+            elif it + m >= max_iter:                              # fixed count: only the final change is reported
+                last = float(reduce_max([v.clone() for v in views]).tolist()[0])
+            if check_tol:
+                for k, c in enumerate(g):
+                    if c < tol:
+                        stop = k
+                        break
+            if stop is not None:
+                if stop + 1 < m:                                  # overshot: replay the chunk up to the stopping iteration
+                    for s, b in zip(slabs, backups):
+                        s._d["phi"].copy_(b)
+                    run(stop + 1, False)
+                it += stop + 1
+                last = g[stop]
+                exchange()
+                break
+            it += m
             exchange()
-            break
-        it += m
-        exchange()
-    for s in slabs:
-        s._lib.b200cfd_poisson_keep_rhs(s._h, 0)
+    finally:
+        for s in slabs:
+            s._lib.b200cfd_poisson_keep_rhs(s._h, 0)
     return it, last

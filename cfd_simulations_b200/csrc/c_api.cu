@@ -55,6 +55,8 @@ struct b200cfd_handle {
     // cached CUDA graph of one time step
     cudaStream_t cap_stream = nullptr;
     cudaGraphExec_t step_graph = nullptr;
+    cudaGraphExec_t multi_graph = nullptr;   // graph_steps consecutive steps in one graph (the step is device-driven, so k steps are k copies)
+    int graph_steps = 8;                     // B200CFD_GRAPH_STEPS; 1 = one graph launch per step
     cudaGraphExec_t begin_graph = nullptr;   // the step without its closing kernel (multi-GPU: all_gather in between)
     cudaGraphExec_t part_graph[2] = {nullptr, nullptr};   // x-slabs: the step up to the finalize of the edge columns / the rest
     int req_halo_l = 0, req_halo_r = 0;      // the halo widths every slab of this decomposition uses (b200cfd_required_halo)
@@ -179,6 +181,7 @@ int b200cfd_destroy(b200cfd_handle* h) {
     if (!h) return B200CFD_OK;
     cudaSetDevice(h->device);
     if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
+    if (h->multi_graph) cudaGraphExecDestroy(h->multi_graph);
     if (h->begin_graph) cudaGraphExecDestroy(h->begin_graph);
     for (cudaGraphExec_t ge : h->part_graph) if (ge) cudaGraphExecDestroy(ge);
     if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
@@ -205,6 +208,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
         h->fuse_k23 = !getenv("B200CFD_NO_FUSE_K23");
         h->fuse_apply = getenv("B200CFD_FUSE_APPLY") != nullptr;
         { const char* e = getenv("B200CFD_FUSE_CORR"); h->fuse_corr = !(e && *e == '0'); }
+        { const char* e = getenv("B200CFD_GRAPH_STEPS"); if (e && atoi(e) >= 1) h->graph_steps = atoi(e); }
         CU(h, cudaSetDevice(h->device));
         launch_tile_flags(h->g, ibm_mask, cylinder_mask, h->flags, nullptr);
         CU(h, cudaDeviceSynchronize());
@@ -214,6 +218,7 @@ int b200cfd_bind_fields(b200cfd_handle* h, void* u, void* v, void* phi, void* u_
                                     : (h->fast ? finalize_fast_num_partials(h->g, h->n_sm) : finalize_num_partials(h->g));
     }
     if (h->step_graph) { cudaGraphExecDestroy(h->step_graph); h->step_graph = nullptr; }
+    if (h->multi_graph) { cudaGraphExecDestroy(h->multi_graph); h->multi_graph = nullptr; }
     if (h->begin_graph) { cudaGraphExecDestroy(h->begin_graph); h->begin_graph = nullptr; }
     for (cudaGraphExec_t& ge : h->part_graph) if (ge) { cudaGraphExecDestroy(ge); ge = nullptr; }
     return B200CFD_OK;
@@ -461,7 +466,24 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
             cudaGraphDestroy(graph);
             if (e != cudaSuccess) { h->step_graph = nullptr; return fail(h, B200CFD_ECUDA, "graph instantiate: %s", cudaGetErrorString(e)); }
         }
-        for (int k = 0; k < n_steps; ++k) CU(h, cudaGraphLaunch(h->step_graph, s));
+        int left = n_steps;
+        // several steps per graph launch: the kernel-to-kernel (programmatic) edges then also span the step boundaries, which
+        // between two graph launches are a full serialisation plus a launch latency
+        const int K = h->graph_steps;
+        if (K > 1 && left >= K) {
+            if (!h->multi_graph) {
+                cudaGraph_t graph = nullptr;
+                CU(h, cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+                for (int k = 0; k < K; ++k) enqueue_step(h, h->cap_stream);
+                cudaError_t e = cudaStreamEndCapture(h->cap_stream, &graph);
+                if (e != cudaSuccess) return fail(h, B200CFD_ECUDA, "graph capture (%d steps): %s", K, cudaGetErrorString(e));
+                e = cudaGraphInstantiate(&h->multi_graph, graph, 0);
+                cudaGraphDestroy(graph);
+                if (e != cudaSuccess) { h->multi_graph = nullptr; return fail(h, B200CFD_ECUDA, "graph instantiate (%d steps): %s", K, cudaGetErrorString(e)); }
+            }
+            for (; left >= K; left -= K) CU(h, cudaGraphLaunch(h->multi_graph, s));
+        }
+        for (int k = 0; k < left; ++k) CU(h, cudaGraphLaunch(h->step_graph, s));
     } else {
         for (int k = 0; k < n_steps; ++k) h->gpu_launches = enqueue_step(h, s);
         CHECK_LAUNCH(h);

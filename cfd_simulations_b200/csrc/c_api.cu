@@ -370,7 +370,7 @@ static bool step_splits(const b200cfd_handle* h) {
 
 // part 0: the whole step.  part 1 / 2 (step_splits only): the step up to and including the finalize of the column blocks
 // at the slab's edges / the finalize of the other column blocks + the closing reduction.
-static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true, int part = 0) {
+static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true, int part = 0, bool after_ctl = false) {
     const b200cfd_config& c = h->cfg;
     const int dt = c.dtype;
     int nl = 0, pi = 0, close_rb1 = 0;
@@ -394,7 +394,7 @@ static int enqueue_step(b200cfd_handle* h, cudaStream_t s, bool close = true, in
         launch_field_sum(dt, h->g, h->nu_t, h->nut_part, s);      // mean(nu_t) for the NEXT step's adaptive dt (v5.py:323)
         nut = h->nu_t; nl += 2;
     }
-    if (h->fast) launch_predictor_fast(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, h->ibm, h->y, h->flags, h->n_sm, s);
+    if (h->fast) launch_predictor_fast(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, h->ibm, h->y, h->flags, h->n_sm, s, after_ctl);
     else launch_predictor(dt, h->g, h->phys, h->ctl, h->u, h->v, h->us, h->vs, h->tau, nut, h->ibm, h->y, s);
     ++nl;
     prof_mark(h, "predictor", s, pi);
@@ -474,7 +474,7 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
             if (!h->multi_graph) {
                 cudaGraph_t graph = nullptr;
                 CU(h, cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
-                for (int k = 0; k < K; ++k) enqueue_step(h, h->cap_stream);
+                for (int k = 0; k < K; ++k) enqueue_step(h, h->cap_stream, true, 0, k > 0);   // k > 0: right behind the control kernel of step k - 1
                 cudaError_t e = cudaStreamEndCapture(h->cap_stream, &graph);
                 if (e != cudaSuccess) return fail(h, B200CFD_ECUDA, "graph capture (%d steps): %s", K, cudaGetErrorString(e));
                 e = cudaGraphInstantiate(&h->multi_graph, graph, 0);
@@ -485,7 +485,7 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
         }
         for (int k = 0; k < left; ++k) CU(h, cudaGraphLaunch(h->step_graph, s));
     } else {
-        for (int k = 0; k < n_steps; ++k) h->gpu_launches = enqueue_step(h, s);
+        for (int k = 0; k < n_steps; ++k) h->gpu_launches = enqueue_step(h, s, true, 0, k > 0);
         CHECK_LAUNCH(h);
     }
     h->step += n_steps;

@@ -28,6 +28,22 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, c
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// the same with the attribute always on (B200CFD_PDL_CTL=0 turns it off): the predictor behind the control kernel
+inline bool pdl_ctl_enabled() {
+    static const bool on = [] { const char* e = getenv("B200CFD_PDL_CTL"); return !(e && *e == '0'); }();
+    return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl_ctl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = (pdl_ctl_enabled() || pdl_enabled()) ? 1 : 0;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // Geometry + precomputed coefficients (host-computed in double with the reference's expressions so
 // the constants are bit-identical to the oracle's: v5.py:131-132,168-169,182-183,205-210).
 struct Geom {
@@ -184,6 +200,10 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 #ifndef B200CFD_PDL_EARLY_TRIGGER
 #define B200CFD_PDL_EARLY_TRIGGER 0   // measured on B200: triggering at kernel entry is SLOWER (4096x1024: 0.332 vs 0.302 ms/step)
 #endif
+// Unconditional release of the dependent launch (used by the one-block control kernel only: the predictor of the next step
+// may then run its prologue - flag tiles, first rows of u, v, which the control kernel does not touch - while the control
+// kernel computes the next dt; the predictor waits right before it reads the control block).
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() {
 #if B200CFD_PDL_EARLY_TRIGGER
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");

@@ -76,9 +76,11 @@ void launch_max_abs2(int dtype, const Geom& g, const void* u, const void* v, Ste
 int tile_flags_dims(const Geom& g, int* ntx, int* nty);     // returns ntx * nty (bytes of the flag map)
 void launch_tile_flags(const Geom& g, const double* ibm, const uint8_t* mask, uint8_t* flags, cudaStream_t s);
 bool fast_path_ok(const Geom& g, const void* const* ptrs, int n);
+// after_ctl: the kernel enqueued right before this one on `s` is this handle's k_ctl_reduce_end (the previous step of the
+// same b200cfd_step call): the launch may then overlap it (programmatic dependent launch, see pdl_release)
 void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
                            void* us, void* vs, void* tau_or_null, const double* ibm, const double* y,
-                           const uint8_t* flags, int n_sm, cudaStream_t s);
+                           const uint8_t* flags, int n_sm, cudaStream_t s, bool after_ctl = false);
 void launch_div_rb1_fast(int dtype, const Geom& g, const void* us, const void* vs, const uint8_t* mask, void* phi,
                          void* div_out, double inv_dt, StepCtl* ctl, const uint8_t* flags, int n_sm, cudaStream_t s);
 // K2 + K3 fused (as executed, omega = 1): div, one red-black iteration, velocity correction, three maxima

@@ -52,6 +52,15 @@ template <> __device__ __forceinline__ D2 ld2<float>(const float* __restrict__ p
     const float2 t = *reinterpret_cast<const float2*>(p + k);
     return D2{(double)t.x, (double)t.y};
 }
+template <typename T> __device__ __forceinline__ D2 ld2cg(const T* __restrict__ p, long long k);
+template <> __device__ __forceinline__ D2 ld2cg<double>(const double* __restrict__ p, long long k) {
+    const double2 t = __ldcg(reinterpret_cast<const double2*>(p + k));
+    return D2{t.x, t.y};
+}
+template <> __device__ __forceinline__ D2 ld2cg<float>(const float* __restrict__ p, long long k) {
+    const float2 t = __ldcg(reinterpret_cast<const float2*>(p + k));
+    return D2{(double)t.x, (double)t.y};
+}
 template <typename T> __device__ __forceinline__ void st2(T* __restrict__ p, long long k, double a, double b);
 template <> __device__ __forceinline__ void st2<double>(double* __restrict__ p, long long k, double a, double b) {
     *reinterpret_cast<double2*>(p + k) = make_double2(a, b);
@@ -130,7 +139,7 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
 // lanes of a warp prefetch the eight 128-byte lines of the row FPF ahead instead of all 32 lanes prefetching twice.
 // predict_fast() is the same function the general rows call, and the two paths agree bit for bit in tests/test_gpu_lean_paths.py.
 template <typename T, bool TAU>
-__device__ __forceinline__ void predictor_rows_lean(const Geom& g, const Phys& p, const double dt, const T* __restrict__ u,
+__device__ __forceinline__ void predictor_rows_lean(const Geom& g, const Phys& p, const StepCtl* __restrict__ ctl, const T* __restrict__ u,
                                                     const T* __restrict__ v, T* __restrict__ us, T* __restrict__ vs,
                                                     T* __restrict__ tau_out, const int lo, const int hi, const int j0) {
     const double half_h = 0.5 * g.hmin, tau_cap = 0.25 * g.hmin * g.hmin / (p.nu_eff + 1e-10);
@@ -138,10 +147,15 @@ __device__ __forceinline__ void predictor_rows_lean(const Geom& g, const Phys& p
     long long k = (long long)lo * pitch + j0;
     D2 U[4], V[4];                                    // rows i-1, i, i+1 and the row in flight: slot (row - lo + 1) & 3
     double UW[2], UE[2], VW[2], VE[2];                // x-neighbours of the lane's column pair: slot (row - lo) & 1
-    U[0] = ld2<T>(u, k - pitch); V[0] = ld2<T>(v, k - pitch);
-    U[1] = ld2<T>(u, k); V[1] = ld2<T>(v, k);
-    U[2] = ld2<T>(u, k + pitch); V[2] = ld2<T>(v, k + pitch);
-    UW[0] = ld(u, k - 1); UE[0] = ld(u, k + 2); VW[0] = ld(v, k - 1); VE[0] = ld(v, k + 2);
+    // The first rows are requested BEFORE the wait for the control kernel (which this kernel may overlap, see pdl_release):
+    // u, v were finished by the finalize kernel before the control kernel started.  ld.global.cg: past L1, whose state under
+    // an overlapped launch is not worth reasoning about for twelve loads.
+    U[0] = ld2cg<T>(u, k - pitch); V[0] = ld2cg<T>(v, k - pitch);
+    U[1] = ld2cg<T>(u, k); V[1] = ld2cg<T>(v, k);
+    U[2] = ld2cg<T>(u, k + pitch); V[2] = ld2cg<T>(v, k + pitch);
+    UW[0] = (double)__ldcg(u + k - 1); UE[0] = (double)__ldcg(u + k + 2); VW[0] = (double)__ldcg(v + k - 1); VE[0] = (double)__ldcg(v + k + 2);
+    pdl_wait();
+    const double dt = ctl->dt;
     const int lane = threadIdx.x & 31;
     const T* pf = (lane < 4 ? u : v) + (long long)(lo + FPF) * pitch + (j0 - 2 * lane) + (lane & 3) * (int)(128 / sizeof(T));
     for (int i4 = lo; i4 < hi; i4 += 4) {
@@ -172,7 +186,8 @@ __global__ void __launch_bounds__(FBT, 5)
 k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __restrict__ u, const T* __restrict__ v,
                  T* __restrict__ us, T* __restrict__ vs, T* __restrict__ tau_out, const double* __restrict__ ibm,
                  const double* __restrict__ y, const uint8_t* __restrict__ flags, int ntx, int rpb, int lean_on) {
-    pdl_wait(); pdl_trigger();
+    // no wait at the top: what precedes this kernel is the one-block control kernel, which releases it at once (pdl_release);
+    // the flag tiles are static and u, v are final, only the control block must be waited for
     const int r0 = blockIdx.y * rpb, r1 = min(r0 + rpb, g.ny);
     const int cb = blockIdx.x * FCOLS;
     const int j0 = cb + 2 * threadIdx.x;
@@ -180,9 +195,10 @@ k_predictor_fast(Geom g, Phys p, const StepCtl* __restrict__ ctl, const T* __res
     // lean rows (see predictor_rows_lean): a block-uniform choice
     if (lean_on && !has_ibm && r0 >= 1 && r1 <= g.ny - 1 && ((r1 - r0) & 3) == 0 &&
         __syncthreads_and(j0 >= 1 && j0 + 2 < g.nx && col_class(g, j0) == COL_INTERIOR && col_class(g, j0 + 1) == COL_INTERIOR)) {
-        predictor_rows_lean<T, TAU>(g, p, ctl->dt, u, v, us, vs, tau_out, r0, r1, j0);
+        predictor_rows_lean<T, TAU>(g, p, ctl, u, v, us, vs, tau_out, r0, r1, j0);
         return;
     }
+    pdl_wait();
     if (j0 >= g.nx) return;
     const int cx = col_class(g, j0), cy = col_class(g, j0 + 1);
     const bool hw = j0 >= 1, he = j0 + 2 < g.nx;             // west / east neighbour columns exist
@@ -289,15 +305,18 @@ bool fast_path_ok(const Geom& g, const void* const* ptrs, int n) {
 
 void launch_predictor_fast(int dtype, const Geom& g, const Phys& p, const StepCtl* ctl, const void* u, const void* v,
                            void* us, void* vs, void* tau, const double* ibm, const double* y, const uint8_t* flags,
-                           int n_sm, cudaStream_t s) {
+                           int n_sm, cudaStream_t s, bool after_ctl) {
     const int rpb = rows_per_block(g, n_sm);
     const dim3 grid((g.nx + FCOLS - 1) / FCOLS, (g.ny + rpb - 1) / rpb);
     const int ntx = (g.nx + FT_W - 1) / FT_W;
-#define PF(T, TAU) launch_pdl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb, lean_on)
+#define PF_ARGS(T) g, p, ctl, (const T*)u, (const T*)v, (T*)us, (T*)vs, (T*)tau, ibm, y, flags, ntx, rpb, lean_on
+#define PF(T, TAU) do { if (after_ctl) launch_pdl_ctl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, PF_ARGS(T)); \
+                        else launch_pdl(k_predictor_fast<T, TAU>, grid, dim3(FBT), s, PF_ARGS(T)); } while (0)
     static const int lean_on = getenv("B200CFD_PRED_LEAN") ? atoi(getenv("B200CFD_PRED_LEAN")) : 1;   // developer knob (A/B)
     if (dtype == 0) { if (tau) PF(double, true); else PF(double, false); }
     else { if (tau) PF(float, true); else PF(float, false); }
 #undef PF
+#undef PF_ARGS
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -388,7 +388,7 @@ __global__ void k_ctl_end_step(StepCtl* c, CtlParams cp, const double* __restric
 __global__ void k_ctl_reduce_end(StepCtl* c, CtlParams cp, const double* __restrict__ ke_part,
                                  const unsigned long long* __restrict__ cnt_part, int n_part, double* red, int close_rb1,
                                  double tol, const double* __restrict__ nut_part, StepScalars* ring, int cap) {
-    pdl_wait(); pdl_trigger();
+    pdl_wait(); pdl_release();
     double loc[RED_N];
     ctl_reduce_local(c, ke_part, cnt_part, n_part, red, close_rb1, tol, nut_part, loc);
     if (threadIdx.x) return;

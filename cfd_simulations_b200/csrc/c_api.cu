@@ -470,7 +470,9 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
         // several steps per graph launch: the kernel-to-kernel (programmatic) edges then also span the step boundaries, which
         // between two graph launches are a full serialisation plus a launch latency
         const int K = h->graph_steps;
-        if (K > 1 && left >= K) {
+        // (built on the first graph call whatever its length: a caller that warms up with a few steps must not find the
+        // capture and instantiation of the long graph inside its timed region)
+        if (K > 1) {
             if (!h->multi_graph) {
                 cudaGraph_t graph = nullptr;
                 CU(h, cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
@@ -480,6 +482,7 @@ int b200cfd_step(b200cfd_handle* h, int n_steps, int use_graph, void* stream) {
                 e = cudaGraphInstantiate(&h->multi_graph, graph, 0);
                 cudaGraphDestroy(graph);
                 if (e != cudaSuccess) { h->multi_graph = nullptr; return fail(h, B200CFD_ECUDA, "graph instantiate (%d steps): %s", K, cudaGetErrorString(e)); }
+                cudaGraphUpload(h->multi_graph, s);          // not on the first timed launch either
             }
             for (; left >= K; left -= K) CU(h, cudaGraphLaunch(h->multi_graph, s));
         }

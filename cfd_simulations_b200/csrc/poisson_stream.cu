@@ -270,7 +270,12 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                         out[m] = pn;
                         // branch-free on purpose: a per-lane `if (owned)` here diverges inside the pipeline body and cost 25% of the
                         // tolerance-mode rate when tried (229 -> 172 GLUPS at 8192^2)
-                        if (CHECK) ch[k / 2] = fmax(ch[k / 2], sel_int(rown, fabs(pn - C[m]) * ownm[m], 0.0));
+                        // (and a compare-and-select instead of fmax(): the library form quiets NaNs in 7-8 instructions; a NaN
+                        // candidate loses the comparison, which is the same outcome)
+                        if (CHECK) {
+                            const double cand = fabs(pn - C[m]) * ownm[m];
+                            ch[k / 2] = (rown && cand > ch[k / 2]) ? cand : ch[k / 2];
+                        }
                     };
                     if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
                     else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }

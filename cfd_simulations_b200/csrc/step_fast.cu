@@ -120,7 +120,9 @@ __device__ __forceinline__ void predict_fast(const Geom& g, double nu_eff, doubl
                                              double uc, double ue, double uw, double un, double us_, double vc, double ve,
                                              double vw, double vn, double vs_, double& ru, double& rv, double& tau_o) {
     const double s = uc * uc + vc * vc;
-    double tau = (s > 1e-20) ? fmin(half_h * rsqrt(s), tau_cap) : dt / 2;
+    // the minimum as a compare-and-select: fmin() is 7-8 instructions on sm_100a (NaN quieting), and no NaN gets here
+    const double hv = half_h * rsqrt(s);
+    double tau = (s > 1e-20) ? (hv < tau_cap ? hv : tau_cap) : dt / 2;
     tau = Rnd<T>::r(tau);
     tau_o = tau;
     const double cu = conv_supg_cell<T>(g, uc, vc, uc, ue, uw, un, us_, tau);

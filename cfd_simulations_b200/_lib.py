@@ -79,7 +79,7 @@ EXPORTS = [
     "b200cfd_k_clean_divergence", "b200cfd_k_predictor",
     "b200cfd_required_halo", "b200cfd_step_begin", "b200cfd_step_end", "b200cfd_reduction_ptr", "b200cfd_reduction_len", "b200cfd_poisson_change_ptr",
     "b200cfd_set_step_global", "b200cfd_pack_columns", "b200cfd_unpack_columns",
-    "b200cfd_step_splits", "b200cfd_step_part", "b200cfd_halo_rows", "b200cfd_jacobi_static",
+    "b200cfd_step_splits", "b200cfd_step_part", "b200cfd_halo_rows", "b200cfd_jacobi_static", "b200cfd_stream_plan_host",
 ]
 
 _lib = None
@@ -116,6 +116,7 @@ def load():
     lib.b200cfd_poisson_info.argtypes = [vp, C.POINTER(C.c_int * 4)]
     lib.b200cfd_poisson_keep_rhs.argtypes = [vp, i32]
     lib.b200cfd_jacobi_static.argtypes = [i32, i32, i32, vp, vp, vp, dbl, dbl, i32, vp]
+    lib.b200cfd_stream_plan_host.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, vp]
     lib.b200cfd_k_supg_tau.argtypes = [vp, vp, vp, vp, dbl, dbl, vp]
     lib.b200cfd_k_convection.argtypes = [vp, vp, vp, vp, vp, vp, i32, vp]
     lib.b200cfd_k_laplacian.argtypes = [vp, vp, vp, dbl, vp]

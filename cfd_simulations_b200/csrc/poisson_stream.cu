@@ -24,6 +24,7 @@
 #include <type_traits>
 
 #include "poisson_tb.h"
+#include "poisson_stream_plan.h"
 #include "tma.cuh"
 
 namespace b200cfd {
@@ -49,6 +50,8 @@ struct StreamParams {
     int OW, H;                // owned columns per strip, halo columns per side
     int tile_h;               // owned rows per row chunk (multiple of 3)
     int n_strips, n_rchunks;
+    int ntile;                // entries of the tile plan (k_stream_plan)
+    int NC;                   // chunk flags per strip (global 3-row chunk ids, see k_stream_make_rhs)
     int own0, own1;           // slab-owned local columns (max|dphi| is taken over them only)
     int jg0;                  // global column of local column 0 (colour parity)
     int nact;                 // active levels of this pass (<= L); the rest pass their input through
@@ -89,6 +92,16 @@ __device__ __forceinline__ double sel_nan(double r, double x, double y) {       
     asm("{\n .reg .pred p;\n setp.nan.f64 p, %1, %1;\n selp.f64 %0, %2, %3, p;\n}" : "=d"(o) : "d"(r), "d"(x), "d"(y));
     return o;
 }
+__device__ __forceinline__ double sel_ge(int a, int b, double x, double y) {                  // a >= b ? x : y   (integers)
+    double o;
+    asm("{\n .reg .pred p;\n setp.ge.s32 p, %1, %2;\n selp.f64 %0, %3, %4, p;\n}" : "=d"(o) : "r"(a), "r"(b), "d"(x), "d"(y));
+    return o;
+}
+__device__ __forceinline__ double sel_gt(int a, int b, double x, double y) {                  // a > b ? x : y    (integers)
+    double o;
+    asm("{\n .reg .pred p;\n setp.gt.s32 p, %1, %2;\n selp.f64 %0, %3, %4, p;\n}" : "=d"(o) : "r"(a), "r"(b), "d"(x), "d"(y));
+    return o;
+}
 __device__ __forceinline__ double sel_int(int c, double x, double y) {                    // c != 0 ? x : y
     double o;
     asm("{\n .reg .pred p;\n setp.ne.s32 p, %1, 0;\n selp.f64 %0, %2, %3, p;\n}" : "=d"(o) : "r"(c), "d"(x), "d"(y));
@@ -98,12 +111,18 @@ __device__ __forceinline__ double sel_int(int c, double x, double y) {          
 // rhs with the cell classes folded in: NaN = masked cell, +Inf = cell that is never updated (array / global border),
 // anything else = div.  The scale (Jacobi: dx^2/dt, v5.py:341; red-black: -1/dt, v5.py:217-219) is applied in double
 // inside the sweep, as the one-sweep kernels do, so both paths round identically in fp32 storage too.
-// tflags[tile] = 1 for every tile whose window (owned cells + halos) contains a special cell: those tiles run the version
-// of the row loop with the class selects.  (Plain stores of the same value: no atomics needed.)
+// cflags[strip * NC + c] = 1 for every 3-row chunk of a strip's window in which some level of the pipeline reads the rhs of a
+// special cell: only those chunks run the version of the chunk body with the class selects.  Chunks are numbered globally:
+// every tile starts ingesting at q0 = r0 - (L + E) with r0 a multiple of 3, so chunk c always holds the phi rows
+// 3c - (L + E) .. + 2, and its levels read the rhs of rows 3c - (L + E) - L .. 3c - (L + E) + 1.  A special cell in row i
+// therefore marks the chunks ceil((i - 1 + L + E) / 3) .. floor((i + 2L + E) / 3).  (Plain stores of the same value: no atomics.)
+// The flag used to be one per TILE; all tiles are resident at once, so the kernel lasted as long as its slowest warp, and
+// a flagged tile (every border tile, the disc) ran 1.7 x the instructions of a plain one over ALL its rows: the r02z capture
+// shows the SMs active for only 69 % of the Jacobi kernel's duration.
 template <typename T>
 __global__ void k_stream_make_rhs(int ny, int nx, long long pitch, int jg0, int nxg, const T* __restrict__ div,
-                                  const uint8_t* __restrict__ mask, T* __restrict__ out, uint8_t* __restrict__ tflags,
-                                  int OW, int H, int tile_h, int VH, int n_strips, int n_rchunks) {
+                                  const uint8_t* __restrict__ mask, T* __restrict__ out, uint8_t* __restrict__ cflags,
+                                  int OW, int H, int L, int LE, int n_strips, int NC) {
     const T nan_t = (T)__longlong_as_double(0x7ff8000000000000ll), inf_t = (T)__longlong_as_double(0x7ff0000000000000ll);
     // four columns (256 apart: coalesced) per thread and trip, loads before stores: the one-element-per-thread form ran at a
     // third of the HBM rate (476 us for 8192^2, as long as a whole 6-sweep pass)
@@ -126,9 +145,9 @@ __global__ void k_stream_make_rhs(int ny, int nx, long long pitch, int jg0, int 
             out[k0 + 256 * q] = !upd ? inf_t : (msk[q] ? nan_t : d[q]);
             if ((!upd || msk[q]) && j < nx) {
                 const int s0 = max((j - H) / OW, 0), s1 = min((j + H) / OW, n_strips - 1);
-                const int c0 = max((i - VH) / tile_h, 0), c1 = min((i + VH) / tile_h, n_rchunks - 1);
+                const int c0 = max((i - 1 + LE + 2) / 3, 0), c1 = min((i + L + LE) / 3, NC - 1);
                 for (int c = c0; c <= c1; ++c)
-                    for (int s = s0; s <= s1; ++s) tflags[c * n_strips + s] = 1;
+                    for (int s = s0; s <= s1; ++s) cflags[s * NC + c] = 1;
             }
         }
     }
@@ -142,7 +161,8 @@ template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
 __global__ void __launch_bounds__(32 * SWARPS, 2)
 k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_rhs,
                  const __grid_constant__ CUtensorMap tm_out, StreamParams P, unsigned long long* __restrict__ slots,
-                 StreamCtl* __restrict__ ctl, int role, int pass_index, const uint8_t* __restrict__ tflags) {
+                 StreamCtl* __restrict__ ctl, int role, int pass_index, const uint8_t* __restrict__ cflags,
+                 const StreamTile* __restrict__ tiles) {
     constexpr int ARR = SKR * SW;                 // elements per slot (3 rows)
     constexpr int KEEP = (L + SKR - 1) / SKR;     // rhs slots behind the current one whose rows are still needed
     constexpr int NSR = NS + KEEP;                // rhs ring: NS slots of lead + the ones the pipeline still reads
@@ -160,7 +180,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tile = blockIdx.x * SWARPS + warp;
-    const bool active = tile < P.n_strips * P.n_rchunks;
+    StreamTile td;                                                // this warp's tile: strip and row range from the cost-balanced plan
+    td.s = 0; td.r0 = 0; td.r1 = 0; td.pad = 0;
+    if (tile < P.ntile) td = tiles[tile];
+    const bool active = td.r1 > td.r0;
     T* ring_p = reinterpret_cast<T*>(smem_raw) + (size_t)warp * WARP_ELEMS;      // phi ring: NS slots
     T* ring_r = ring_p + NS * ARR;                                               // rhs ring: NSR slots
     T* stage = ring_r + NSR * ARR;                                               // 2 x 3 output rows (dense, OW per row)
@@ -175,11 +198,11 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
             mbar_fence_init();
         }
         __syncwarp();
-        const int s = tile % P.n_strips, rc = tile / P.n_strips;
+        const int s = td.s;
         const int x0 = s * P.OW;                                  // first owned column
         const int jw0 = x0 - P.H;                                 // window origin (multiple of 4; may be negative)
         const int c0 = jw0 + SPL * lane;
-        const int r0 = rc * P.tile_h, r1 = min(r0 + P.tile_h, P.ny);
+        const int r0 = td.r0, r1 = td.r1;                        // r0 is a multiple of 3; r1 is one or ny
         // ingest rows q0 .. ; the row leaving level L at ingest step q is q - L.  q0 is chosen so that (i) level L's first
         // valid row (q0 + L) is <= r0 and (ii) row r0 leaves the pipeline (at ingest step r0 + L) as the FIRST row of a chunk
         // (stores are whole 3-row boxes): q0 = r0 - L - e with (2L + e) % 3 == 0
@@ -226,124 +249,142 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         // special - computed it: redundant halo copies stay bit-identical to the owner's value)
         const double q4 = 0.25 * nscale, axd = ax * dinv, ayd = ay * dinv, nsd = nscale * dinv;
 
-        // The row loop, in two versions chosen per tile (warp-uniform): SPECIAL tiles contain masked cells, never-updated
-        // border cells or inactive levels and carry the class selects; plain tiles (almost all of them) are pure arithmetic.
-        auto run = [&](auto special_tag) {
-            constexpr bool SPECIAL = decltype(special_tag)::value;
-            // red-black: which cells of a row have the colour of a level is a compile-time fact once the parity PB of
-            // (first row of the chunk + colour offset of the window) is fixed; the chunk body exists in both parities and a
-            // warp-uniform branch picks one per chunk (a branch per LEVEL gets if-converted: both arms issue, predicated)
-            // one level: row `row` of sweep k+1 from rows S (row-1), C (row), N (row+1) of sweep k and the rhs of `row`.
-            // Straight-line code: shuffles are unconditional, the parts that do not depend on the x-neighbours come first.
-            auto level = [&](auto pb_tag, int k, int jrow, int row, const double (&S)[SPL], const double (&C)[SPL],
-                             const double (&N)[SPL], const T* rhs_row, double (&out)[SPL]) {
-                constexpr int PB = decltype(pb_tag)::value;
-                double r[SPL];
-                SRow<T>::ld(rhs_row, r);
-                const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
-                const int act = k < nact;                               // warp-uniform (always true in plain tiles)
-                if (MODE == 0) {
+        // The chunk body exists in three versions, chosen per 3-row chunk (warp-uniform): VAR 0, plain chunks (almost all of
+        // them), pure arithmetic; VAR 1, chunks in which some level reads the rhs of a masked or never-updated cell, with the
+        // class selects; VAR 2, passes with inactive levels (the last, shallower pass of a solve and redo passes), with the
+        // class selects and the pass-through of the inactive levels.  All three compute an updated cell's value with the same
+        // operations in the same order, so a value does not depend on which version produced it.
+        // red-black: which cells of a row have the colour of a level is a compile-time fact once the parity PB of
+        // (first row of the chunk + colour offset of the window) is fixed; the chunk body exists in both parities and a
+        // warp-uniform branch picks one per chunk (a branch per LEVEL gets if-converted: both arms issue, predicated)
+        // one level: row `row` of sweep k+1 from rows S (row-1), C (row), N (row+1) of sweep k and the rhs of `row`.
+        // Straight-line code: shuffles are unconditional, the parts that do not depend on the x-neighbours come first.
+        auto level = [&](auto pb_tag, auto var_tag, int k, int jrow, int row, const double (&S)[SPL], const double (&C)[SPL],
+                         const double (&N)[SPL], const T* rhs_row, double (&out)[SPL]) {
+            constexpr int PB = decltype(pb_tag)::value;
+            constexpr int VAR = decltype(var_tag)::value;
+            constexpr int SENT = 0x7ff00000;                        // high word of +Inf.  The sentinels are +Inf and the positive quiet NaN, so a
+            // SIGNED compare of the high word tells them from every finite value (negative values are negative integers)
+            double r[SPL];
+            SRow<T>::ld(rhs_row, r);
+            const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
+            const int act = k < nact;                               // warp-uniform (always true unless VAR == 2)
+            if (MODE == 0) {
 #pragma unroll
-                    for (int m = 0; m < SPL; ++m) {
-                        const double ns = N[m] + S[m], rq = r[m] * q4;
-                        const double e = m < SPL - 1 ? C[(m + 1) % SPL] : En, w = m > 0 ? C[(m + SPL - 1) % SPL] : Wn;
-                        const double v = Rnd<T>::r(fma(0.25, (e + w) + ns, rq));
-                        if (SPECIAL) {
-                            // updated cell -> v, masked (NaN) -> 0 (v5.py:345), never-updated border (+Inf) -> kept
-                            const double o = sel_lt(fabs(r[m]), INF, v, sel_nan(r[m], 0.0, C[m]));
-                            out[m] = sel_int(act, o, C[m]);
-                        } else out[m] = v;
-                    }
-                } else {
-                    // colour of level k: even k = first colour ((i + j) odd, v5.py:215), odd k = second.  c0 is a multiple
-                    // of 4, so cells 0, 2 have the parity of (row + jg0) and cells 1, 3 the other one (warp-uniform branch).
-                    // row = q + jrow with (q + colpar) & 1 == PB, jrow = j - 1 - k a compile-time offset
-                    const int want = (k & 1) ? 0 : 1;
-                    const bool even_cells = (((PB + jrow) % 2 + 2) % 2) == want;       // compile time
-                    const int rown = row >= r0 && row < r1;
-                    auto cell = [&](int m, double e, double w) {
-                        const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
-                        double pn = fma(axd, e + w, t);
-                        if (SOR) pn = fma(omega, pn - C[m], C[m]);
-                        pn = Rnd<T>::r(pn);
-                        if (SPECIAL) pn = sel_int(act, sel_lt(fabs(r[m]), INF, pn, C[m]), C[m]);   // masked / border / inactive: kept
-                        out[m] = pn;
-                        // branch-free on purpose: a per-lane `if (owned)` here diverges inside the pipeline body and cost 25% of the
-                        // tolerance-mode rate when tried (229 -> 172 GLUPS at 8192^2)
-                        // (and a compare-and-select instead of fmax(): the library form quiets NaNs in 7-8 instructions; a NaN
-                        // candidate loses the comparison, which is the same outcome)
-                        if (CHECK) {
-                            const double cand = fabs(pn - C[m]) * ownm[m];
-                            ch[k / 2] = (rown && cand > ch[k / 2]) ? cand : ch[k / 2];
-                        }
-                    };
-                    if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
-                    else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }
+                for (int m = 0; m < SPL; ++m) {
+                    const double ns = N[m] + S[m], rq = r[m] * q4;
+                    const double e = m < SPL - 1 ? C[(m + 1) % SPL] : En, w = m > 0 ? C[(m + SPL - 1) % SPL] : Wn;
+                    const double v = Rnd<T>::r(fma(0.25, (e + w) + ns, rq));
+                    if (VAR == 2) {
+                        // updated cell -> v, masked (NaN) -> 0 (v5.py:345), never-updated border (+Inf) -> kept
+                        const double o = sel_lt(fabs(r[m]), INF, v, sel_nan(r[m], 0.0, C[m]));
+                        out[m] = sel_int(act, o, C[m]);
+                    } else if (VAR == 1) {
+                        // the same classes, told apart on the high word with integer compares (off the fp64 pipe and ready
+                        // long before v).  Level 1 zeroes the masked cells; in the levels behind it a masked cell already
+                        // holds 0, so "keep" covers both classes there.
+                        const int a = __double2hiint(r[m]);
+                        out[m] = k == 0 ? sel_ge(a, SENT, sel_gt(a, SENT, 0.0, C[m]), v) : sel_ge(a, SENT, C[m], v);
+                    } else out[m] = v;
                 }
-            };
-            int nstore = 0;
-            for (int k = 0; k < NCH; ++k) {
-                const int slot = k % NS;
-                mbar_wait(&bars[slot], (uint32_t)((k / NS) & 1));
-                const T* sp = ring_p + slot * ARR + SPL * lane;
-                const int q = q0 + SKR * k;
-                T* sg = stage + (nstore & 1) * ARR;
-                // rhs rows of the chunks k, k-1, ... (this lane's columns): the level that computes row q + j - 1 - lv reads
-                // row (j - 1 - lv) mod 3 of chunk k + floor((j - 1 - lv) / 3), all compile-time offsets
-                const T* rb[KEEP + 2];
-                {
-                    const int km = k % NSR;
-#pragma unroll
-                    for (int o = 0; o < KEEP + 2; ++o) { int sl = km - o; if (sl < 0) sl += NSR; rb[o] = ring_rl + sl * ARR; }
-                }
-                const int orow = q - L;                                  // first row leaving the pipeline in this chunk
-                const bool do_store = orow >= r0 && orow < r1;          // whole chunks by construction
-                if (do_store && nstore >= 2) {                           // the staging buffer's previous TMA store has read it
-                    if (lane == 0) tma_store_wait_read<1>();
-                    __syncwarp();
-                }
-                auto body = [&](auto pb_tag) {
-#pragma unroll
-                    for (int j = 0; j < SKR; ++j) {
-                        // ring row j of this slot = phi row q + j enters level 1 as its north row
-                        SRow<T>::ld(sp + j * SW, R[0][(j + 2) % 3]);
-#pragma unroll
-                        for (int lv = 0; lv < L; ++lv) {
-                            const int row = q + j - 1 - lv;                  // row computed by level lv + 1
-                            const int off = j - 1 - lv;                      // compile time after unrolling
-                            const int back = off >= 0 ? 0 : (-off + SKR - 1) / SKR, jr = off + back * SKR;
-                            if (lv + 1 < L) {
-                                // the level writes straight into the next level's north row (no copy: the ncu source page
-                                // of the first version showed a quarter of the issue slots going to register moves)
-                                level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW,
-                                      R[lv + 1 < L ? lv + 1 : lv][(j + 2) % 3]);
-                            } else {
-                                double out[SPL];
-                                level(pb_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
-                                if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
-                            }
-                        }
+            } else {
+                // colour of level k: even k = first colour ((i + j) odd, v5.py:215), odd k = second.  c0 is a multiple
+                // of 4, so cells 0, 2 have the parity of (row + jg0) and cells 1, 3 the other one (warp-uniform branch).
+                // row = q + jrow with (q + colpar) & 1 == PB, jrow = j - 1 - k a compile-time offset
+                const int want = (k & 1) ? 0 : 1;
+                const bool even_cells = (((PB + jrow) % 2 + 2) % 2) == want;       // compile time
+                const int rown = row >= r0 && row < r1;
+                auto cell = [&](int m, double e, double w) {
+                    const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
+                    double pn = fma(axd, e + w, t);
+                    if (SOR) pn = fma(omega, pn - C[m], C[m]);
+                    pn = Rnd<T>::r(pn);
+                    if (VAR == 2) pn = sel_int(act, sel_lt(fabs(r[m]), INF, pn, C[m]), C[m]);   // masked / border / inactive: kept
+                    else if (VAR == 1) pn = sel_ge(__double2hiint(r[m]), SENT, C[m], pn);   // masked / border: kept
+                    out[m] = pn;
+                    // branch-free on purpose: a per-lane `if (owned)` here diverges inside the pipeline body and cost 25% of the
+                    // tolerance-mode rate when tried (229 -> 172 GLUPS at 8192^2)
+                    // (and a compare-and-select instead of fmax(): the library form quiets NaNs in 7-8 instructions; a NaN
+                    // candidate loses the comparison, which is the same outcome)
+                    if (CHECK) {
+                        const double cand = fabs(pn - C[m]) * ownm[m];
+                        ch[k / 2] = (rown && cand > ch[k / 2]) ? cand : ch[k / 2];
                     }
                 };
-                if (MODE == 1 && ((q + colpar) & 1)) body(std::integral_constant<int, 1>{});
-                else body(std::integral_constant<int, 0>{});
-                if (do_store) {
-                    fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0) {
-                        tma_store_2d(&tm_out, x0, orow, sg);             // 3 dense rows of the OW owned columns
-                        tma_store_commit();
-                    }
-                    ++nstore;
-                }
-                __syncwarp();
-                // the phi slot of chunk k is free now; the rhs of chunk k + NS overwrites that of chunk k - KEEP, which no
-                // level reads any more (level L of the next chunk reaches back to chunk k + 1 - KEEP)
-                if (lane == 0 && k + NS < NCH) issue(k + NS);
+                if (even_cells) { out[1] = C[1]; out[3] = C[3]; cell(0, C[1], Wn); cell(2, C[3], C[1]); }
+                else { out[0] = C[0]; out[2] = C[2]; cell(1, C[2], C[0]); cell(3, En, C[2]); }
             }
         };
-        const bool special = nact < L || (tflags != nullptr && tflags[tile] != 0);
-        if (special) run(std::true_type{}); else run(std::false_type{});
+        const bool inactive = nact < L;
+        const uint8_t* cf = cflags + (size_t)s * P.NC + r0 / SKR;   // chunk k of this tile is global chunk r0 / 3 + k
+        int cf_cur = cf[0];
+        int nstore = 0;
+        for (int k = 0; k < NCH; ++k) {
+            const int slot = k % NS;
+            const int cf_next = k + 1 < NCH ? (int)cf[k + 1] : 0;        // a chunk ahead: the load has a whole chunk to arrive
+            mbar_wait(&bars[slot], (uint32_t)((k / NS) & 1));
+            const T* sp = ring_p + slot * ARR + SPL * lane;
+            const int q = q0 + SKR * k;
+            T* sg = stage + (nstore & 1) * ARR;
+            // rhs rows of the chunks k, k-1, ... (this lane's columns): the level that computes row q + j - 1 - lv reads
+            // row (j - 1 - lv) mod 3 of chunk k + floor((j - 1 - lv) / 3), all compile-time offsets
+            const T* rb[KEEP + 2];
+            {
+                const int km = k % NSR;
+#pragma unroll
+                for (int o = 0; o < KEEP + 2; ++o) { int sl = km - o; if (sl < 0) sl += NSR; rb[o] = ring_rl + sl * ARR; }
+            }
+            const int orow = q - L;                                  // first row leaving the pipeline in this chunk
+            const bool do_store = orow >= r0 && orow < r1;          // whole chunks by construction
+            if (do_store && nstore >= 2) {                           // the staging buffer's previous TMA store has read it
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+            }
+            auto body = [&](auto pb_tag, auto var_tag) {
+#pragma unroll
+                for (int j = 0; j < SKR; ++j) {
+                    // ring row j of this slot = phi row q + j enters level 1 as its north row
+                    SRow<T>::ld(sp + j * SW, R[0][(j + 2) % 3]);
+#pragma unroll
+                    for (int lv = 0; lv < L; ++lv) {
+                        const int row = q + j - 1 - lv;                  // row computed by level lv + 1
+                        const int off = j - 1 - lv;                      // compile time after unrolling
+                        const int back = off >= 0 ? 0 : (-off + SKR - 1) / SKR, jr = off + back * SKR;
+                        if (lv + 1 < L) {
+                            // the level writes straight into the next level's north row (no copy: the ncu source page
+                            // of the first version showed a quarter of the issue slots going to register moves)
+                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW,
+                                  R[lv + 1 < L ? lv + 1 : lv][(j + 2) % 3]);
+                        } else {
+                            double out[SPL];
+                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
+                            if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
+                        }
+                    }
+                }
+            };
+            auto variants = [&](auto pb_tag) {
+                if (inactive) body(pb_tag, std::integral_constant<int, 2>{});
+                else if (cf_cur) body(pb_tag, std::integral_constant<int, 1>{});
+                else body(pb_tag, std::integral_constant<int, 0>{});
+            };
+            if (MODE == 1 && ((q + colpar) & 1)) variants(std::integral_constant<int, 1>{});
+            else variants(std::integral_constant<int, 0>{});
+            cf_cur = cf_next;
+            if (do_store) {
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_2d(&tm_out, x0, orow, sg);             // 3 dense rows of the OW owned columns
+                    tma_store_commit();
+                }
+                ++nstore;
+            }
+            __syncwarp();
+            // the phi slot of chunk k is free now; the rhs of chunk k + NS overwrites that of chunk k - KEEP, which no
+            // level reads any more (level L of the next chunk reaches back to chunk k + 1 - KEEP)
+            if (lane == 0 && k + NS < NCH) issue(k + NS);
+        }
         if (lane == 0) tma_store_wait<0>();
     }
     // ---- per-iteration max|dphi| over the owned cells -> slots; the last block closes the pass
@@ -392,6 +433,16 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     }
 }
 
+// The tile plan (poisson_stream_plan.h), one thread per strip; the allocation of tiles to strips is a short serial step.
+__global__ void k_stream_plan(StreamPlanArgs a, long long* __restrict__ cost, int* __restrict__ n, int* __restrict__ first,
+                              StreamTile* __restrict__ tiles) {
+    for (int s = threadIdx.x; s < a.n_strips; s += blockDim.x) cost[s] = plan_strip_cost(a, s);
+    __syncthreads();
+    if (threadIdx.x == 0) plan_allocate(a, cost, n, first);
+    __syncthreads();
+    for (int s = threadIdx.x; s < a.n_strips; s += blockDim.x) plan_cut(a, s, cost[s], n[s], first[s], tiles);
+}
+
 // ---- host side -----------------------------------------------------------------------------------------------------
 struct PoissonStream {
     void* rhs_s = nullptr;
@@ -399,12 +450,17 @@ struct PoissonStream {
     size_t bytes = 0;
     unsigned long long* slots = nullptr;   // 8 entries
     StreamCtl* ctl = nullptr;
-    uint8_t* tflags = nullptr;             // one byte per tile: its window contains masked / never-updated cells
-    size_t tflags_cap = 0;
-    // what rhs_s / tflags were built from: a caller that solves in chunks on an UNCHANGED right-hand side (the slab solver:
+    uint8_t* cflags = nullptr;             // one byte per (strip, global 3-row chunk): its levels read masked / never-updated cells
+    size_t cflags_cap = 0;
+    StreamTile* tiles = nullptr;           // the cost-balanced tile plan built from cflags
+    size_t tiles_cap = 0;
+    long long* plan_cost = nullptr; int* plan_n = nullptr;   // per strip: cost, tiles, first tile (plan_n holds both int arrays)
+    size_t plan_cap = 0;
+    int plan_ntile = 0, plan_alpha = -1;
+    // what rhs_s / cflags were built from: a caller that solves in chunks on an UNCHANGED right-hand side (the slab solver:
     // a few iterations, halo refresh, a few more) declares it with poisson_stream_keep_rhs and skips the rebuild
     const void* rhs_src = nullptr; const void* mask_src = nullptr;
-    int rhs_ny = 0, rhs_nx = 0, rhs_L = 0, rhs_tile_h = 0, rhs_dtype = -1;
+    int rhs_ny = 0, rhs_nx = 0, rhs_L = 0, rhs_dtype = -1;
     bool keep_rhs = false;
     int last_depth = 0, last_passes = 0;
 };
@@ -412,7 +468,7 @@ static std::string g_stream_err;
 const char* poisson_stream_error() { return g_stream_err.c_str(); }
 void poisson_stream_destroy(PoissonStream* ps) {
     if (!ps) return;
-    cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->tflags);
+    cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->cflags); cudaFree(ps->tiles); cudaFree(ps->plan_cost); cudaFree(ps->plan_n);
     delete ps;
 }
 void poisson_stream_keep_rhs(PoissonStream** pps, int keep) {
@@ -431,7 +487,7 @@ static int env_int(const char* name, int dflt) {
 
 template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
 static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
-                         unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
+                         unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* cflags, const StreamTile* tiles, cudaStream_t s) {
     constexpr int KEEP = (L + SKR - 1) / SKR;
     const size_t smem = (size_t)SWARPS * (NS + NS + KEEP + 2) * SKR * SW * sizeof(T) + SWARPS * NS * sizeof(uint64_t);
     auto kern = k_poisson_stream<T, MODE, L, NS, SOR, CHECK>;
@@ -442,8 +498,8 @@ static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUt
         }
         configured = true;
     }
-    const int ntile = P.n_strips * P.n_rchunks;
-    kern<<<(ntile + SWARPS - 1) / SWARPS, 32 * SWARPS, smem, s>>>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags);
+    const int ntile = P.ntile;
+    kern<<<(ntile + SWARPS - 1) / SWARPS, 32 * SWARPS, smem, s>>>(mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles);
     if (cudaPeekAtLastError() != cudaSuccess) { g_stream_err = cudaGetErrorString(cudaGetLastError()); return -1; }
     return 0;
 }
@@ -452,21 +508,21 @@ static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUt
 #define STREAM_NS 2
 template <typename T, int MODE, bool SOR, bool CHECK>
 static int stream_depth(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
-                        unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
-    if (L <= 2) return stream_launch<T, MODE, 2, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
-    return stream_launch<T, MODE, 6, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+                        unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* cflags, const StreamTile* tiles, cudaStream_t s) {
+    if (L <= 2) return stream_launch<T, MODE, 2, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s);
+    return stream_launch<T, MODE, 6, STREAM_NS, SOR, CHECK>(mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s);
 }
 template <typename T, int MODE>
 static int stream_dispatch(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
-                           unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* tflags, cudaStream_t s) {
+                           unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* cflags, const StreamTile* tiles, cudaStream_t s) {
     if constexpr (MODE == 0) {
-        return stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+        return stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s);
     } else {
         const bool sor = P.omega != 1.0, chk = slots != nullptr;
-        if (sor) return chk ? stream_depth<T, MODE, true, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
-                            : stream_depth<T, MODE, true, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
-        return chk ? stream_depth<T, MODE, false, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s)
-                   : stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, tflags, s);
+        if (sor) return chk ? stream_depth<T, MODE, true, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s)
+                            : stream_depth<T, MODE, true, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s);
+        return chk ? stream_depth<T, MODE, false, true>(L, mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s)
+                   : stream_depth<T, MODE, false, false>(L, mi, mr, mo, P, slots, ctl, role, pass_index, cflags, tiles, s);
     }
 }
 
@@ -514,35 +570,62 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     P.H = (L + 3) / 4 * 4;
     P.OW = SW - 2 * P.H;
     P.n_strips = (g.nx + P.OW - 1) / P.OW;
-    // row chunks: every tile resident at once (one warp per tile); ~6 warps per SM
+    // tiles: every tile resident at once (one warp per tile), 8 warps per SM; the plan kernel below cuts the strips into
+    // ntile row ranges of equal cost (at least 4 groups of 3 rows each)
     const int want = env_int("B200CFD_STREAM_WARPS_PER_SM", 8) * n_sm;
-    int nrc = want / P.n_strips;
-    if (nrc < 1) nrc = 1;
-    int th = (g.ny + nrc - 1) / nrc;
-    th = (th + SKR - 1) / SKR * SKR;
-    if (th < 4 * SKR) th = 4 * SKR;
-    P.tile_h = th;
-    P.n_rchunks = (g.ny + th - 1) / th;
+    const int G = (g.ny + SKR - 1) / SKR, min_groups = 4;
+    int per_strip_max = G / min_groups;
+    if (per_strip_max < 1) per_strip_max = 1;
+    long long nt = want;
+    if (nt > (long long)P.n_strips * per_strip_max) nt = (long long)P.n_strips * per_strip_max;
+    if (nt < P.n_strips) nt = P.n_strips;
+    P.ntile = (int)nt;
+    P.n_rchunks = (P.ntile + P.n_strips - 1) / P.n_strips;        // informational: average tiles per strip
+    P.tile_h = (g.ny + P.n_rchunks - 1) / P.n_rchunks;             // informational
     const long long n = (long long)g.ny * g.pitch;
     const int nb = (int)((n + 255) / 256 < 148 * 32 ? (n + 255) / 256 : 148 * 32);
-    const size_t ntile = (size_t)P.n_strips * P.n_rchunks;
-    if (ps->tflags_cap < ntile) {
-        cudaFree(ps->tflags); ps->tflags = nullptr; ps->tflags_cap = 0;
-        if (cudaMalloc(&ps->tflags, ntile) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(tile flags)"; return -1; }
-        ps->tflags_cap = ntile;
+    const int E = (3 - (2 * L) % 3) % 3;                            // the kernel's E: every tile starts ingesting at r0 - (L + E)
+    P.NC = (g.ny + 2 * L + E) / SKR + 2;                            // global chunk ids 0 .. NC - 1 cover every tile's last chunk
+    const size_t nflag = (size_t)P.n_strips * P.NC;
+    if (ps->cflags_cap < nflag) {
+        cudaFree(ps->cflags); ps->cflags = nullptr; ps->cflags_cap = 0; ps->rhs_src = nullptr;
+        if (cudaMalloc(&ps->cflags, nflag) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(chunk flags)"; return -1; }
+        ps->cflags_cap = nflag;
     }
+    // (the flags depend on the strip geometry and the chunk phase, both functions of L, not on the row chunking)
+    if (ps->tiles_cap < (size_t)P.ntile) {
+        cudaFree(ps->tiles); ps->tiles = nullptr; ps->tiles_cap = 0; ps->rhs_src = nullptr;
+        if (cudaMalloc(&ps->tiles, (size_t)P.ntile * sizeof(StreamTile)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(tile plan)"; return -1; }
+        ps->tiles_cap = (size_t)P.ntile;
+    }
+    if (ps->plan_cap < (size_t)P.n_strips) {
+        cudaFree(ps->plan_cost); cudaFree(ps->plan_n); ps->plan_cost = nullptr; ps->plan_n = nullptr; ps->plan_cap = 0; ps->rhs_src = nullptr;
+        if (cudaMalloc(&ps->plan_cost, (size_t)P.n_strips * sizeof(long long)) != cudaSuccess ||
+            cudaMalloc(&ps->plan_n, 2 * (size_t)P.n_strips * sizeof(int)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(plan scratch)"; return -1; }
+        ps->plan_cap = (size_t)P.n_strips;
+    }
+    // extra cost of a chunk with class selects, percent of a plain chunk (instruction counts of the two chunk bodies: 1.39 / 1.25)
+    const int alpha = env_int("B200CFD_STREAM_ALPHA", mode == 0 ? 35 : 20);
     const bool reuse = ps->keep_rhs && ps->rhs_src == div && ps->mask_src == (const void*)mask && ps->rhs_ny == g.ny &&
-                       ps->rhs_nx == g.nx && ps->rhs_L == L && ps->rhs_tile_h == P.tile_h && ps->rhs_dtype == dtype;
-    const int VH = L + 3;                                           // rows above / below a chunk its pipeline touches
+                       ps->rhs_nx == g.nx && ps->rhs_L == L && ps->rhs_dtype == dtype && ps->plan_ntile == P.ntile && ps->plan_alpha == alpha;
     const dim3 gnb((unsigned)((g.pitch + 1023) / 1024), (unsigned)(g.ny < 2048 ? g.ny : 2048));
     (void)nb;
-    if (reuse) { /* rhs_s and tflags still describe this right-hand side */ }
-    else if (cudaMemsetAsync(ps->tflags, 0, ntile, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile flags)"; return -1; }
+    if (reuse) { /* rhs_s and cflags still describe this right-hand side */ }
+    else if (cudaMemsetAsync(ps->cflags, 0, nflag, s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(chunk flags)"; return -1; }
     else if (dtype == 0) k_stream_make_rhs<double><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const double*)div, mask, (double*)ps->rhs_s,
-                                                                  ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
+                                                                  ps->cflags, P.OW, P.H, L, L + E, P.n_strips, P.NC);
     else k_stream_make_rhs<float><<<gnb, 256, 0, s>>>(g.ny, g.nx, g.pitch, g.jg0, g.nxg, (const float*)div, mask, (float*)ps->rhs_s,
-                                                    ps->tflags, P.OW, P.H, P.tile_h, VH, P.n_strips, P.n_rchunks);
-    ps->rhs_src = div; ps->mask_src = mask; ps->rhs_ny = g.ny; ps->rhs_nx = g.nx; ps->rhs_L = L; ps->rhs_tile_h = P.tile_h; ps->rhs_dtype = dtype;
+                                                    ps->cflags, P.OW, P.H, L, L + E, P.n_strips, P.NC);
+    if (!reuse) {
+        StreamPlanArgs pa;
+        pa.cflags = ps->cflags; pa.n_strips = P.n_strips; pa.NC = P.NC; pa.ny = g.ny; pa.shift = (2 * L + E) / SKR;
+        pa.ntile = P.ntile; pa.alpha_pct = alpha; pa.min_groups = min_groups;
+        if (cudaMemsetAsync(ps->tiles, 0, (size_t)P.ntile * sizeof(StreamTile), s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile plan)"; return -1; }
+        k_stream_plan<<<1, 256, 0, s>>>(pa, ps->plan_cost, ps->plan_n, ps->plan_n + P.n_strips, ps->tiles);
+        if (cudaPeekAtLastError() != cudaSuccess) { g_stream_err = cudaGetErrorString(cudaGetLastError()); return -1; }
+    }
+    ps->rhs_src = div; ps->mask_src = mask; ps->rhs_ny = g.ny; ps->rhs_nx = g.nx; ps->rhs_L = L; ps->rhs_dtype = dtype;
+    ps->plan_ntile = P.ntile; ps->plan_alpha = alpha;
     CUtensorMap m_phi, m_alt, m_rhs, o_phi, o_alt;
     if (!tma_make_2d(&m_phi, dtype, phi, g.nx, g.ny, g.pitch, SW, SKR) || !tma_make_2d(&m_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, SW, SKR) ||
         !tma_make_2d(&m_rhs, dtype, ps->rhs_s, g.nx, g.ny, g.pitch, SW, SKR) ||
@@ -566,10 +649,10 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         const CUtensorMap& mo = cur == phi ? o_alt : o_phi;
         unsigned long long* sl = check ? ps->slots : nullptr;
         StreamCtl* ct = check ? ps->ctl : nullptr;
-        if (dtype == 0) return mode == 0 ? stream_dispatch<double, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s)
-                                         : stream_dispatch<double, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s);
-        return mode == 0 ? stream_dispatch<float, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s)
-                         : stream_dispatch<float, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->tflags, s);
+        if (dtype == 0) return mode == 0 ? stream_dispatch<double, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->cflags, ps->tiles, s)
+                                         : stream_dispatch<double, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->cflags, ps->tiles, s);
+        return mode == 0 ? stream_dispatch<float, 0>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->cflags, ps->tiles, s)
+                         : stream_dispatch<float, 1>(L, mi, m_rhs, mo, P, sl, ct, role, pass, ps->cflags, ps->tiles, s);
     };
     StreamCtl hc;
     bool stopped = false;
@@ -602,3 +685,24 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
 }
 
 }  // namespace b200cfd
+
+// Host run of the tile plan (the same functions k_stream_plan runs, poisson_stream_plan.h), for the CPU test-suite: no CUDA call.
+// cflags: [n_strips][NC] host bytes; tiles_out: ntile x 4 ints (strip, r0, r1, 0).  Returns 0, or -1 on bad arguments.
+extern "C" int b200cfd_stream_plan_host(const uint8_t* cflags, int n_strips, int NC, int ny, int shift, int ntile, int alpha_pct,
+                                        int min_groups, int* tiles_out) {
+    using namespace b200cfd;
+    if (!cflags || !tiles_out || n_strips < 1 || NC < 1 || ny < 1 || ntile < n_strips || min_groups < 1 || shift < 0) return -1;
+    StreamPlanArgs a;
+    a.cflags = cflags; a.n_strips = n_strips; a.NC = NC; a.ny = ny; a.shift = shift; a.ntile = ntile; a.alpha_pct = alpha_pct;
+    a.min_groups = min_groups;
+    long long* cost = new long long[n_strips];
+    int* n = new int[2 * n_strips];
+    StreamTile* t = reinterpret_cast<StreamTile*>(tiles_out);
+    for (int i = 0; i < 4 * ntile; ++i) tiles_out[i] = 0;
+    for (int s = 0; s < n_strips; ++s) cost[s] = plan_strip_cost(a, s);
+    plan_allocate(a, cost, n, n + n_strips);
+    for (int s = 0; s < n_strips; ++s) plan_cut(a, s, cost[s], n[s], n[n_strips + s], t);
+    delete[] cost; delete[] n;
+    return 0;
+}
+

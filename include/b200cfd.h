@@ -222,6 +222,15 @@ int b200cfd_k_predictor(b200cfd_handle* h, const void* u, const void* v, void* u
 int b200cfd_jacobi_static(int dtype, int ny, int nx, void* phi, const void* rhs_div, const uint8_t* mask,
                           double dx, double dt, int sweeps, void* stream);
 
+/* ---- test hook (host only, no CUDA call) ----
+ * The cost-balanced tile plan of the streaming Poisson kernel (csrc/poisson_stream_plan.h), run on the host with the code
+ * the device runs.  No counterpart in the reference (v5.py:202-226 and :336-346 sweep the whole array in one prange); it
+ * exists so that the CPU test-suite can check the plan's invariants: every strip's rows covered exactly once, cuts on
+ * multiples of 3, at most `ntile` tiles.  cflags: [n_strips][NC] bytes (1 = the chunk runs the class selects);
+ * tiles_out: ntile x 4 ints (strip, first row, one past the last row, 0; first == last: unused entry). */
+int b200cfd_stream_plan_host(const uint8_t* cflags, int n_strips, int NC, int ny, int shift, int ntile, int alpha_pct,
+                             int min_groups, int* tiles_out);
+
 #ifdef __cplusplus
 }
 #endif

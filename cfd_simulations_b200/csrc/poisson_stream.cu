@@ -34,6 +34,14 @@ namespace b200cfd {
 #define SWARPS 4      // warps (independent tiles) per block
 #define SKR 3         // rows per ring slot = unroll of the row loop
 #define FULLM 0xffffffffu
+// A/B switches (tools/build_variant.sh): shuffle the centre row at the point of use (the round-2 form) instead of the north
+// row one row step early; red-black levels load only the two rhs values they use (two LDS.64) instead of the whole 4-cell row
+#ifndef STREAM_LATE_SHFL
+#define STREAM_LATE_SHFL 0
+#endif
+#ifndef STREAM_RB_LDS64
+#define STREAM_RB_LDS64 0
+#endif
 
 struct StreamCtl {            // device-resident control of a tolerance-terminated solve
     int done;                 // tolerance reached: every later launch exits at once
@@ -242,6 +250,17 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
                 for (int m = 0; m < SPL; ++m) R[k][j][m] = 0.0;
 
+        // x-neighbours of each level's CENTRE row, shuffled one row step early: a level's north row becomes its centre row in
+        // the next row step, so the level shuffles the end cells of its north row now and uses the result a whole row step
+        // later.  Shuffling the centre row at the point of use left the ~24-cycle shuffle latency exposed in every level: the
+        // r04a capture has 2.5 of the 5.3 stall cycles per instruction on the short scoreboard, sampled on the first
+        // consumers of the shuffles.  Same values, same operations: results are bit-identical.
+        // (Jacobi needs both neighbours; a red-black level updates cells 0, 2 or cells 1, 3 and needs only the west or
+        // only the east one, and the parity alternates from row to row, so it keeps the one the NEXT row step uses.)
+        double NbW[L], NbE[L];
+#pragma unroll
+        for (int k = 0; k < L; ++k) { NbW[k] = 0.0; NbE[k] = 0.0; }
+
         const int scol = SPL * lane - P.H;                          // this lane's first column inside the staged (owned) row
         const bool st_lane = scol >= 0 && scol + SPL <= P.OW;
         const T* ring_rl = ring_r + SPL * lane;
@@ -258,18 +277,24 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         // (first row of the chunk + colour offset of the window) is fixed; the chunk body exists in both parities and a
         // warp-uniform branch picks one per chunk (a branch per LEVEL gets if-converted: both arms issue, predicated)
         // one level: row `row` of sweep k+1 from rows S (row-1), C (row), N (row+1) of sweep k and the rhs of `row`.
-        // Straight-line code: shuffles are unconditional, the parts that do not depend on the x-neighbours come first.
+        // Straight-line code: the shuffles (of the NORTH row, for the next row step: see NbW / NbE) are unconditional.
         auto level = [&](auto pb_tag, auto var_tag, int k, int jrow, int row, const double (&S)[SPL], const double (&C)[SPL],
                          const double (&N)[SPL], const T* rhs_row, double (&out)[SPL]) {
             constexpr int PB = decltype(pb_tag)::value;
             constexpr int VAR = decltype(var_tag)::value;
             constexpr int SENT = 0x7ff00000;                        // high word of +Inf.  The sentinels are +Inf and the positive quiet NaN, so a
             // SIGNED compare of the high word tells them from every finite value (negative values are negative integers)
-            double r[SPL];
-            SRow<T>::ld(rhs_row, r);
-            const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
+            double r[SPL] = {0.0, 0.0, 0.0, 0.0};
+            if (MODE == 0 || !STREAM_RB_LDS64) SRow<T>::ld(rhs_row, r);
             const int act = k < nact;                               // warp-uniform (always true unless VAR == 2)
             if (MODE == 0) {
+#if STREAM_LATE_SHFL
+                const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
+#else
+                const double Wn = NbW[k], En = NbE[k];             // neighbours of C, shuffled during the previous row step
+                NbW[k] = __shfl_up_sync(FULLM, N[3], 1);           // neighbours of N = the next row step's C
+                NbE[k] = __shfl_down_sync(FULLM, N[0], 1);
+#endif
 #pragma unroll
                 for (int m = 0; m < SPL; ++m) {
                     const double ns = N[m] + S[m], rq = r[m] * q4;
@@ -294,6 +319,18 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 const int want = (k & 1) ? 0 : 1;
                 const bool even_cells = (((PB + jrow) % 2 + 2) % 2) == want;       // compile time
                 const int rown = row >= r0 && row < r1;
+                // this row step uses the west neighbour (cells 0, 2) or the east one (cells 1, 3); the next one the other
+#if STREAM_LATE_SHFL
+                const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
+#else
+                const double Wn = NbW[k], En = NbE[k];
+                if (even_cells) NbE[k] = __shfl_down_sync(FULLM, N[0], 1);
+                else NbW[k] = __shfl_up_sync(FULLM, N[3], 1);
+#endif
+                if (STREAM_RB_LDS64) {
+                    if (even_cells) { r[0] = (double)rhs_row[0]; r[2] = (double)rhs_row[2]; }
+                    else { r[1] = (double)rhs_row[1]; r[3] = (double)rhs_row[3]; }
+                }
                 auto cell = [&](int m, double e, double w) {
                     const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
                     double pn = fma(axd, e + w, t);
@@ -433,14 +470,52 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     }
 }
 
-// The tile plan (poisson_stream_plan.h), one thread per strip; the allocation of tiles to strips is a short serial step.
-__global__ void k_stream_plan(StreamPlanArgs a, long long* __restrict__ cost, int* __restrict__ n, int* __restrict__ first,
-                              StreamTile* __restrict__ tiles) {
-    for (int s = threadIdx.x; s < a.n_strips; s += blockDim.x) cost[s] = plan_strip_cost(a, s);
+// The tile plan (poisson_stream_plan.h): one block, the items of every phase spread over its threads.
+// seg: [n_strips][nseg] segment sums -> exclusive prefixes; cost, n, first: per strip.
+__global__ void __launch_bounds__(1024)
+k_stream_plan(StreamPlanArgs a, int* __restrict__ seg, int* __restrict__ cost, int* __restrict__ n, int* __restrict__ first,
+              StreamTile* __restrict__ tiles) {
+    __shared__ int s_lo, s_hi, s_sum;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const int nseg = plan_nseg(a), cap = plan_cap(a);
+    for (int it = tid; it < a.n_strips * nseg; it += nt) seg[it] = plan_seg_sum(a, it / nseg, it % nseg);
+    if (tid == 0) { s_lo = 1; s_hi = 1; }
     __syncthreads();
-    if (threadIdx.x == 0) plan_allocate(a, cost, n, first);
+    for (int s = tid; s < a.n_strips; s += nt) {
+        const int c = plan_strip_prefix(a, seg + (size_t)s * nseg);
+        cost[s] = c;
+        atomicMax(&s_hi, c);
+    }
     __syncthreads();
-    for (int s = threadIdx.x; s < a.n_strips; s += blockDim.x) plan_cut(a, s, cost[s], n[s], first[s], tiles);
+    // the smallest T with sum_s tiles_at(cost[s], T) <= ntile (bisection; every strip evaluates its own term)
+    while (true) {
+        const int lo = s_lo, hi = s_hi;
+        if (lo >= hi) break;
+        const int mid = lo + (hi - lo) / 2;
+        __syncthreads();
+        if (tid == 0) s_sum = 0;
+        __syncthreads();
+        int local = 0;
+        for (int s = tid; s < a.n_strips; s += nt) local += plan_tiles_at(cost[s], mid, cap);
+        if (local) atomicAdd(&s_sum, local);
+        __syncthreads();
+        if (tid == 0) { if (s_sum <= a.ntile) s_hi = mid; else s_lo = mid + 1; }
+        __syncthreads();
+    }
+    const int T = s_lo;
+    for (int s = tid; s < a.n_strips; s += nt) n[s] = plan_tiles_at(cost[s], T, cap);
+    __syncthreads();
+    if (tid == 0) { int f = 0; for (int s = 0; s < a.n_strips; ++s) { first[s] = f; f += n[s]; } }
+    __syncthreads();
+    // one warp per strip, one lane per tile
+    for (int s = tid / 32; s < a.n_strips; s += nt / 32)
+        for (int j = tid % 32; j < n[s]; j += 32) {
+            StreamTile t;
+            t.s = s; t.pad = 0;
+            t.r0 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j);
+            t.r1 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j + 1);
+            if (first[s] + j < a.ntile) tiles[first[s] + j] = t;
+        }
 }
 
 // ---- host side -----------------------------------------------------------------------------------------------------
@@ -454,7 +529,7 @@ struct PoissonStream {
     size_t cflags_cap = 0;
     StreamTile* tiles = nullptr;           // the cost-balanced tile plan built from cflags
     size_t tiles_cap = 0;
-    long long* plan_cost = nullptr; int* plan_n = nullptr;   // per strip: cost, tiles, first tile (plan_n holds both int arrays)
+    int* plan_i = nullptr;                 // plan scratch: per strip cost, tiles, first tile; then [n_strips][nseg] segment sums
     size_t plan_cap = 0;
     int plan_ntile = 0, plan_alpha = -1;
     // what rhs_s / cflags were built from: a caller that solves in chunks on an UNCHANGED right-hand side (the slab solver:
@@ -468,7 +543,7 @@ static std::string g_stream_err;
 const char* poisson_stream_error() { return g_stream_err.c_str(); }
 void poisson_stream_destroy(PoissonStream* ps) {
     if (!ps) return;
-    cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->cflags); cudaFree(ps->tiles); cudaFree(ps->plan_cost); cudaFree(ps->plan_n);
+    cudaFree(ps->rhs_s); cudaFree(ps->alt); cudaFree(ps->slots); cudaFree(ps->ctl); cudaFree(ps->cflags); cudaFree(ps->tiles); cudaFree(ps->plan_i);
     delete ps;
 }
 void poisson_stream_keep_rhs(PoissonStream** pps, int keep) {
@@ -574,7 +649,7 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     // ntile row ranges of equal cost (at least 4 groups of 3 rows each)
     const int want = env_int("B200CFD_STREAM_WARPS_PER_SM", 8) * n_sm;
     const int G = (g.ny + SKR - 1) / SKR, min_groups = 4;
-    int per_strip_max = G / min_groups;
+    int per_strip_max = G / min_groups;                            // (the plan's own cap, which knows alpha, is tighter)
     if (per_strip_max < 1) per_strip_max = 1;
     long long nt = want;
     if (nt > (long long)P.n_strips * per_strip_max) nt = (long long)P.n_strips * per_strip_max;
@@ -598,14 +673,16 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         if (cudaMalloc(&ps->tiles, (size_t)P.ntile * sizeof(StreamTile)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(tile plan)"; return -1; }
         ps->tiles_cap = (size_t)P.ntile;
     }
-    if (ps->plan_cap < (size_t)P.n_strips) {
-        cudaFree(ps->plan_cost); cudaFree(ps->plan_n); ps->plan_cost = nullptr; ps->plan_n = nullptr; ps->plan_cap = 0; ps->rhs_src = nullptr;
-        if (cudaMalloc(&ps->plan_cost, (size_t)P.n_strips * sizeof(long long)) != cudaSuccess ||
-            cudaMalloc(&ps->plan_n, 2 * (size_t)P.n_strips * sizeof(int)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(plan scratch)"; return -1; }
-        ps->plan_cap = (size_t)P.n_strips;
+    const size_t plan_ints = (size_t)P.n_strips * (3 + (size_t)((G + PLAN_SEG - 1) / PLAN_SEG));
+    if (ps->plan_cap < plan_ints) {
+        cudaFree(ps->plan_i); ps->plan_i = nullptr; ps->plan_cap = 0; ps->rhs_src = nullptr;
+        if (cudaMalloc(&ps->plan_i, plan_ints * sizeof(int)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(plan scratch)"; return -1; }
+        ps->plan_cap = plan_ints;
     }
     // extra cost of a chunk with class selects, percent of a plain chunk (instruction counts of the two chunk bodies: 1.39 / 1.25)
-    const int alpha = env_int("B200CFD_STREAM_ALPHA", mode == 0 ? 35 : 20);
+    int alpha = env_int("B200CFD_STREAM_ALPHA", mode == 0 ? 35 : 20);
+    if (alpha < 0) alpha = 0;
+    if (alpha > 400) alpha = 400;
     const bool reuse = ps->keep_rhs && ps->rhs_src == div && ps->mask_src == (const void*)mask && ps->rhs_ny == g.ny &&
                        ps->rhs_nx == g.nx && ps->rhs_L == L && ps->rhs_dtype == dtype && ps->plan_ntile == P.ntile && ps->plan_alpha == alpha;
     const dim3 gnb((unsigned)((g.pitch + 1023) / 1024), (unsigned)(g.ny < 2048 ? g.ny : 2048));
@@ -621,7 +698,8 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         pa.cflags = ps->cflags; pa.n_strips = P.n_strips; pa.NC = P.NC; pa.ny = g.ny; pa.shift = (2 * L + E) / SKR;
         pa.ntile = P.ntile; pa.alpha_pct = alpha; pa.min_groups = min_groups;
         if (cudaMemsetAsync(ps->tiles, 0, (size_t)P.ntile * sizeof(StreamTile), s) != cudaSuccess) { g_stream_err = "cudaMemsetAsync(tile plan)"; return -1; }
-        k_stream_plan<<<1, 256, 0, s>>>(pa, ps->plan_cost, ps->plan_n, ps->plan_n + P.n_strips, ps->tiles);
+        k_stream_plan<<<1, 1024, 0, s>>>(pa, ps->plan_i + 3 * (size_t)P.n_strips, ps->plan_i, ps->plan_i + P.n_strips, ps->plan_i + 2 * (size_t)P.n_strips,
+                                         ps->tiles);
         if (cudaPeekAtLastError() != cudaSuccess) { g_stream_err = cudaGetErrorString(cudaGetLastError()); return -1; }
     }
     ps->rhs_src = div; ps->mask_src = mask; ps->rhs_ny = g.ny; ps->rhs_nx = g.nx; ps->rhs_L = L; ps->rhs_dtype = dtype;
@@ -691,18 +769,37 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
 extern "C" int b200cfd_stream_plan_host(const uint8_t* cflags, int n_strips, int NC, int ny, int shift, int ntile, int alpha_pct,
                                         int min_groups, int* tiles_out) {
     using namespace b200cfd;
-    if (!cflags || !tiles_out || n_strips < 1 || NC < 1 || ny < 1 || ntile < n_strips || min_groups < 1 || shift < 0) return -1;
+    if (!cflags || !tiles_out || n_strips < 1 || NC < 1 || ny < 1 || ntile < n_strips || min_groups < 1 || shift < 0 ||
+        alpha_pct < 0 || alpha_pct > 400) return -1;
     StreamPlanArgs a;
     a.cflags = cflags; a.n_strips = n_strips; a.NC = NC; a.ny = ny; a.shift = shift; a.ntile = ntile; a.alpha_pct = alpha_pct;
     a.min_groups = min_groups;
-    long long* cost = new long long[n_strips];
-    int* n = new int[2 * n_strips];
+    const int nseg = plan_nseg(a), cap = plan_cap(a);
+    int* seg = new int[(size_t)n_strips * nseg];
+    int* cost = new int[3 * (size_t)n_strips];
+    int* n = cost + n_strips;
+    int* first = n + n_strips;
     StreamTile* t = reinterpret_cast<StreamTile*>(tiles_out);
     for (int i = 0; i < 4 * ntile; ++i) tiles_out[i] = 0;
-    for (int s = 0; s < n_strips; ++s) cost[s] = plan_strip_cost(a, s);
-    plan_allocate(a, cost, n, n + n_strips);
-    for (int s = 0; s < n_strips; ++s) plan_cut(a, s, cost[s], n[s], n[n_strips + s], t);
-    delete[] cost; delete[] n;
+    for (int it = 0; it < n_strips * nseg; ++it) seg[it] = plan_seg_sum(a, it / nseg, it % nseg);
+    int lo = 1, hi = 1;
+    for (int s = 0; s < n_strips; ++s) { cost[s] = plan_strip_prefix(a, seg + (size_t)s * nseg); if (cost[s] > hi) hi = cost[s]; }
+    while (lo < hi) {
+        const int mid = lo + (hi - lo) / 2;
+        int sum = 0;
+        for (int s = 0; s < n_strips; ++s) sum += plan_tiles_at(cost[s], mid, cap);
+        if (sum <= ntile) hi = mid; else lo = mid + 1;
+    }
+    int f = 0;
+    for (int s = 0; s < n_strips; ++s) { n[s] = plan_tiles_at(cost[s], lo, cap); first[s] = f; f += n[s]; }
+    for (int s = 0; s < n_strips; ++s)
+        for (int j = 0; j < n[s]; ++j) {
+            StreamTile& d = t[first[s] + j];
+            d.s = s; d.pad = 0;
+            d.r0 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j);
+            d.r1 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j + 1);
+        }
+    delete[] seg; delete[] cost;
     return 0;
 }
 

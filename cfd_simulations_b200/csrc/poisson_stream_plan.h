@@ -7,8 +7,10 @@
 // capture showed the SMs active for 69 % of the Jacobi kernel's duration.  The plan therefore gives every strip a number of
 // tiles in proportion to its cost and cuts each strip where the running cost crosses equal shares.
 //
-// The functions are __host__ __device__ and sequential per strip: the device runs them with one thread per strip
-// (k_stream_plan), the CPU test-suite runs the same code through b200cfd_stream_plan_host.
+// The functions are __host__ __device__ and each handles one item (a segment of a strip, a strip, a tile): the device runs
+// them with the items spread over the threads of one block (k_stream_plan), the CPU test-suite runs the same functions in
+// loops through b200cfd_stream_plan_host.  (A first version ran serially per strip, with the allocation on one thread in
+// 64-bit arithmetic: 0.8 ms at 8192^2, as long as two passes of the kernel it plans.)
 // No counterpart in the reference (v5.py:202-226, :336-346 sweep the whole array in one Numba prange).
 #pragma once
 #include <stdint.h>
@@ -29,11 +31,20 @@ struct StreamPlanArgs {
     int ny;
     int shift;               // rows 3g .. 3g + 2 leave the pipeline in global chunk g + shift  (shift = (2L + E) / 3)
     int ntile;               // tiles to hand out (= warps resident at once)
-    int alpha_pct;           // extra cost of a flagged chunk, in percent of a plain one
-    int min_groups;          // fewest 3-row groups a tile may own
+    int alpha_pct;           // extra cost of a flagged chunk, in percent of a plain one (0 .. 400)
+    int min_groups;          // fewest 3-row groups a tile may own (guaranteed through plan_cap)
 };
 
 PLAN_HD inline int plan_groups(const StreamPlanArgs& a) { return (a.ny + 2) / 3; }
+constexpr int PLAN_SEG = 64;                                          // groups per segment of a strip
+PLAN_HD inline int plan_nseg(const StreamPlanArgs& a) { return (plan_groups(a) + PLAN_SEG - 1) / PLAN_SEG; }
+// most tiles a strip may get: a tile's share of its strip's cost is at least 100 G / cap, a group costs at most
+// 100 + alpha_pct, so with cap <= 100 G / ((100 + alpha_pct) min_groups) every tile owns at least min_groups groups
+// without any further rule
+PLAN_HD inline int plan_cap(const StreamPlanArgs& a) {
+    const long long cap = 100ll * plan_groups(a) / ((100ll + a.alpha_pct) * a.min_groups);
+    return cap < 1 ? 1 : (int)cap;
+}
 
 PLAN_HD inline int plan_group_cost(const StreamPlanArgs& a, int s, int g) {
     int c = g + a.shift;
@@ -41,71 +52,49 @@ PLAN_HD inline int plan_group_cost(const StreamPlanArgs& a, int s, int g) {
     return 100 + (a.cflags[(size_t)s * a.NC + c] ? a.alpha_pct : 0);
 }
 
-// cost of strip s (percent units)
-PLAN_HD inline long long plan_strip_cost(const StreamPlanArgs& a, int s) {
+// item (strip, segment): cost of the segment's groups (percent units)
+PLAN_HD inline int plan_seg_sum(const StreamPlanArgs& a, int s, int seg) {
     const int G = plan_groups(a);
-    long long t = 0;
-    for (int g = 0; g < G; ++g) t += plan_group_cost(a, s, g);
+    int g1 = (seg + 1) * PLAN_SEG;
+    if (g1 > G) g1 = G;
+    int t = 0;
+    for (int g = seg * PLAN_SEG; g < g1; ++g) t += plan_group_cost(a, s, g);
     return t;
 }
 
-// tiles per strip: the allocation that minimises the most expensive tile, max_s cost[s] / n[s], subject to sum n[s] <= ntile
-// (bisection on that maximum T: n[s] = ceil(cost[s] / T)), every strip at least one tile, none more than G / min_groups;
-// tiles left over go to the strips with the highest cost per tile.  first[s] = index of strip s's first tile.
-// Serial; n_strips is small (74 at 8192 columns).
-PLAN_HD inline void plan_allocate(const StreamPlanArgs& a, const long long* cost, int* n, int* first) {
-    const int G = plan_groups(a);
-    int cap = G / a.min_groups;
-    if (cap < 1) cap = 1;
-    long long lo = 1, hi = 1;
-    for (int s = 0; s < a.n_strips; ++s) if (cost[s] > hi) hi = cost[s];
-    while (lo < hi) {
-        const long long mid = lo + (hi - lo) / 2;
-        long long need = 0;
-        for (int s = 0; s < a.n_strips; ++s) {
-            long long k = (cost[s] + mid - 1) / mid;
-            if (k < 1) k = 1;
-            if (k > cap) k = cap;
-            need += k;
-        }
-        if (need <= a.ntile) hi = mid; else lo = mid + 1;
-    }
-    int used = 0;
-    for (int s = 0; s < a.n_strips; ++s) {
-        long long k = (cost[s] + lo - 1) / lo;
-        if (k < 1) k = 1;
-        if (k > cap) k = cap;
-        n[s] = (int)k;
-        used += n[s];
-    }
-    for (int spare = a.ntile - used; spare > 0; --spare) {
-        int best = -1;
-        for (int s = 0; s < a.n_strips; ++s)
-            if (n[s] < cap && (best < 0 || cost[s] * n[best] > cost[best] * n[s])) best = s;
-        if (best < 0) break;
-        ++n[best];
-    }
-    int f = 0;
-    for (int s = 0; s < a.n_strips; ++s) { first[s] = f; f += n[s]; }
+// item strip: turns the strip's segment sums into exclusive prefix sums in place; returns the strip's cost
+PLAN_HD inline int plan_strip_prefix(const StreamPlanArgs& a, int* seg) {
+    const int n = plan_nseg(a);
+    int acc = 0;
+    for (int i = 0; i < n; ++i) { const int v = seg[i]; seg[i] = acc; acc += v; }
+    return acc;
 }
 
-// cuts strip s into n tiles of (nearly) equal cost; entries that cannot be filled (short grids) are left empty
-PLAN_HD inline void plan_cut(const StreamPlanArgs& a, int s, long long cost, int n, int first, StreamTile* tiles) {
-    const int G = plan_groups(a);
-    // the fixed cost of a tile (filling its pipeline) is the same for all and does not move the cuts
-    long long acc = 0;
-    int j = 0, start = 0;
-    for (int g = 0; g < G && j < n - 1; ++g) {
+// tiles a strip of this cost gets when no tile may cost more than T
+PLAN_HD inline int plan_tiles_at(int cost, int T, int cap) {
+    int k = (int)(((unsigned)cost + (unsigned)T - 1u) / (unsigned)T);
+    if (k < 1) k = 1;
+    if (k > cap) k = cap;
+    return k;
+}
+
+// item (strip, tile j of n): first owned row of the tile = 3 x (number of leading groups whose cost stays below j / n of the
+// strip's); pre = the strip's exclusive segment prefix sums.  j == n gives ny (one past the last tile's rows).
+PLAN_HD inline int plan_cut_row(const StreamPlanArgs& a, int s, const int* pre, int cost, int n, int j) {
+    if (j <= 0) return 0;
+    if (j >= n) return a.ny;
+    const int G = plan_groups(a), nseg = plan_nseg(a);
+    const int thr = (int)(((long long)j * cost + n - 1) / n);         // first g with acc(g) >= thr closes tile j - 1
+    int seg = 0;
+    while (seg + 1 < nseg && pre[seg + 1] < thr) ++seg;
+    int acc = pre[seg], g = seg * PLAN_SEG;
+    for (; g < G; ++g) {
         acc += plan_group_cost(a, s, g);
-        const int len = g + 1 - start, left = G - (g + 1);
-        if (acc * n >= (long long)(j + 1) * cost && len >= a.min_groups && left >= (n - 1 - j) * a.min_groups) {
-            tiles[first + j].s = s; tiles[first + j].r0 = 3 * start; tiles[first + j].r1 = 3 * (g + 1); tiles[first + j].pad = 0;
-            start = g + 1;
-            ++j;
-        }
+        if (acc >= thr) break;
     }
-    tiles[first + j].s = s; tiles[first + j].r0 = 3 * start; tiles[first + j].r1 = a.ny; tiles[first + j].pad = 0;
-    for (++j; j < n; ++j) { tiles[first + j].s = s; tiles[first + j].r0 = 0; tiles[first + j].r1 = 0; tiles[first + j].pad = 0; }
+    int row = 3 * (g + 1);
+    if (row > a.ny) row = a.ny;
+    return row;
 }
 
 }  // namespace b200cfd

@@ -61,7 +61,7 @@ def check_partition(tiles, n_strips, ny, min_groups=4):
         assert np.all(t[:, 1] % 3 == 0)
         assert np.all(t[:-1, 2] % 3 == 0)
         if len(t) > 1:
-            assert np.all(t[:, 2] - t[:, 1] >= 3 * min_groups - 2)
+            assert np.all(t[:, 2] - t[:, 1] >= 3 * (min_groups - 1))
     return live
 
 
@@ -92,7 +92,7 @@ def test_chunk_flag_range_matches_the_pipeline_walk():
             assert set(range(c0, c1 + 1)) == want, (L, i)
 
 
-@pytest.mark.parametrize("alpha", [0, 20, 35, 60])
+@pytest.mark.parametrize("alpha", [0, 20, 35, 60, 100, 150])
 def test_plan_8192_square_is_a_balanced_partition(alpha):
     ny = nx = 8192
     L = 6
@@ -111,10 +111,11 @@ def test_plan_8192_square_is_a_balanced_partition(alpha):
     ntile = 8 * 148
     tiles = run_plan(flags, n_strips, NC, ny, shift, ntile, alpha)
     live = check_partition(tiles, n_strips, ny)
-    assert len(live) == ntile
+    # (tiles the minimax allocation has no use for stay empty: one more tile for SOME of the equal strips would not lower the maximum)
+    assert ntile - n_strips < len(live) <= ntile
     cost = tile_costs(live, flags, shift, alpha)
     # whole tiles per strip: 1184 tiles over 74 strips of slightly different cost leave some strips with 15 and some with 16
-    assert cost.max() / cost.mean() < 1.08, cost.max() / cost.mean()
+    assert cost.max() / (cost.sum() / ntile) < 1.08, cost.max() / (cost.sum() / ntile)
     # ... and no allocation does better: with one tile fewer in total the most expensive tile could not get cheaper
     strip_cost = np.array([cost[live[:, 0] == s].sum() for s in range(n_strips)])
     n_s = np.array([np.sum(live[:, 0] == s) for s in range(n_strips)])

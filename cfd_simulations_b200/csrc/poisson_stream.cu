@@ -31,13 +31,29 @@ namespace b200cfd {
 
 #define SW 128        // window width = TMA box width
 #define SPL 4         // columns per lane
+#ifndef SWARPS
 #define SWARPS 4      // warps (independent tiles) per block
+#endif
+#ifndef STREAM_MINB
+#define STREAM_MINB 2 // blocks per SM the kernel is compiled for (registers) and the plan fills (SWARPS * STREAM_MINB tiles per SM)
+#endif
 #define SKR 3         // rows per ring slot = unroll of the row loop
 #define FULLM 0xffffffffu
-// A/B switches (tools/build_variant.sh): shuffle the centre row at the point of use (the round-2 form) instead of the north
-// row one row step early; red-black levels load only the two rhs values they use (two LDS.64) instead of the whole 4-cell row
-#ifndef STREAM_LATE_SHFL
-#define STREAM_LATE_SHFL 0
+// A/B switches (tools/build_variant.sh): shuffle the north row one row step early (see NbW / NbE) instead of the centre row
+// at the point of use, per mode; red-black levels load only the two rhs values they use (two LDS.64) instead of the whole
+// 4-cell row.  Measured at 8192^2 (profiles/r04b_alpha.txt): early shuffles cost Jacobi 4 % (964 -> 924 GLUPS, 8 more
+// registers) and gain SOR 4 % (461 -> 480); LDS.64 is within the noise (+2 % SOR, -1 % GS).
+#ifndef STREAM_EARLY_SHFL_J
+#define STREAM_EARLY_SHFL_J 0
+#endif
+#ifndef STREAM_EARLY_SHFL_RB
+#define STREAM_EARLY_SHFL_RB 1
+#endif
+#ifndef STREAM_STAGE1
+#define STREAM_STAGE1 0   // one staging buffer for the output rows instead of two (3 KB less shared memory per warp)
+#endif
+#ifndef STREAM_SWZ
+#define STREAM_SWZ 1      // fp64: phi and rhs rows land in shared memory with TMA's 32-byte swizzle (conflict-free 128-bit row loads)
 #endif
 #ifndef STREAM_RB_LDS64
 #define STREAM_RB_LDS64 0
@@ -73,6 +89,12 @@ template <> struct SRow<double> {
         const double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
         o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
     }
+    // row written by a swizzled TMA box (tma_make_3d_swz32): sw = 2 for the lanes whose 32-byte unit lies in an odd 128-byte
+    // line (lane bit 2), where the unit's two 16-byte halves are exchanged; 0 otherwise
+    static __device__ __forceinline__ void ld_swz(const double* p, int sw, double (&o)[SPL]) {
+        const double2 a = *reinterpret_cast<const double2*>(p + sw), b = *reinterpret_cast<const double2*>(p + 2 - sw);
+        o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+    }
     static __device__ __forceinline__ void st(double* p, const double (&x)[SPL]) {
         *reinterpret_cast<double2*>(p) = make_double2(x[0], x[1]);
         *reinterpret_cast<double2*>(p + 2) = make_double2(x[2], x[3]);
@@ -83,6 +105,7 @@ template <> struct SRow<float> {
         const float4 t = *reinterpret_cast<const float4*>(p);
         o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
     }
+    static __device__ __forceinline__ void ld_swz(const float* p, int, double (&o)[SPL]) { ld(p, o); }   // (one 128-bit load per lane: no conflicts)
     static __device__ __forceinline__ void st(float* p, const double (&x)[SPL]) {
         *reinterpret_cast<float4*>(p) = make_float4((float)x[0], (float)x[1], (float)x[2], (float)x[3]);
     }
@@ -166,7 +189,7 @@ __global__ void k_stream_make_rhs(int ny, int nx, long long pitch, int jg0, int 
 // SOR: omega != 1 (the relaxation step is compiled in only then: omega = 1 must stay the exact Gauss-Seidel update).
 // CHECK: accumulate the per-iteration max|dphi| (tolerance mode).
 template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
-__global__ void __launch_bounds__(32 * SWARPS, 2)
+__global__ void __launch_bounds__(32 * SWARPS, STREAM_MINB)
 k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constant__ CUtensorMap tm_rhs,
                  const __grid_constant__ CUtensorMap tm_out, StreamParams P, unsigned long long* __restrict__ slots,
                  StreamCtl* __restrict__ ctl, int role, int pass_index, const uint8_t* __restrict__ cflags,
@@ -174,8 +197,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     constexpr int ARR = SKR * SW;                 // elements per slot (3 rows)
     constexpr int KEEP = (L + SKR - 1) / SKR;     // rhs slots behind the current one whose rows are still needed
     constexpr int NSR = NS + KEEP;                // rhs ring: NS slots of lead + the ones the pipeline still reads
-    constexpr int WARP_ELEMS = (NS + NSR + 2) * ARR;   // phi ring, rhs ring, 2 staging buffers of 3 output rows
-    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int NSTG = STREAM_STAGE1 ? 1 : 2;
+    constexpr bool SWZ = STREAM_SWZ && sizeof(T) == 8;
+    constexpr int WARP_ELEMS = (NS + NSR + NSTG) * ARR;   // phi ring, rhs ring, staging buffers of 3 output rows
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
     int nact = P.nact;
     if (ctl) {
         const int done = *reinterpret_cast<volatile int*>(&ctl->done);
@@ -222,8 +247,13 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         auto issue = [&](int k) {
             const int slot = k % NS;
             mbar_expect_tx(&bars[slot], (uint32_t)(2 * ARR * sizeof(T)));
-            tma_load_2d(ring_p + slot * ARR, &tm_in, jw0, q0 + SKR * k, &bars[slot]);
-            tma_load_2d(ring_r + (k % NSR) * ARR, &tm_rhs, jw0, q0 + SKR * k, &bars[slot]);
+            if (SWZ) {                                            // 3-D swizzled view: (0, x / 4, y); jw0 is a multiple of 4
+                tma_load_3d(ring_p + slot * ARR, &tm_in, 0, jw0 / 4, q0 + SKR * k, &bars[slot]);
+                tma_load_3d(ring_r + (k % NSR) * ARR, &tm_rhs, 0, jw0 / 4, q0 + SKR * k, &bars[slot]);
+            } else {
+                tma_load_2d(ring_p + slot * ARR, &tm_in, jw0, q0 + SKR * k, &bars[slot]);
+                tma_load_2d(ring_r + (k % NSR) * ARR, &tm_rhs, jw0, q0 + SKR * k, &bars[slot]);
+            }
         };
         if (lane == 0) {
             const int n0 = NCH < NS ? NCH : NS;
@@ -250,11 +280,11 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
                 for (int m = 0; m < SPL; ++m) R[k][j][m] = 0.0;
 
-        // x-neighbours of each level's CENTRE row, shuffled one row step early: a level's north row becomes its centre row in
-        // the next row step, so the level shuffles the end cells of its north row now and uses the result a whole row step
-        // later.  Shuffling the centre row at the point of use left the ~24-cycle shuffle latency exposed in every level: the
-        // r04a capture has 2.5 of the 5.3 stall cycles per instruction on the short scoreboard, sampled on the first
-        // consumers of the shuffles.  Same values, same operations: results are bit-identical.
+        // x-neighbours of each level's CENTRE row, optionally shuffled one row step early (STREAM_EARLY_SHFL_*): a level's north
+        // row becomes its centre row in the next row step, so the level can shuffle the end cells of its north row now and use
+        // the result a whole row step later.  Same values, same operations: results are bit-identical.  It pays for the
+        // red-black levels only (see the switches at the top); the r04a capture has 2.5 of the 5.3 stall cycles per
+        // instruction on the short scoreboard, but the SASS already had 17+ instructions between a shuffle and its first use.
         // (Jacobi needs both neighbours; a red-black level updates cells 0, 2 or cells 1, 3 and needs only the west or
         // only the east one, and the parity alternates from row to row, so it keeps the one the NEXT row step uses.)
         double NbW[L], NbE[L];
@@ -264,6 +294,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         const int scol = SPL * lane - P.H;                          // this lane's first column inside the staged (owned) row
         const bool st_lane = scol >= 0 && scol + SPL <= P.OW;
         const T* ring_rl = ring_r + SPL * lane;
+        const int swz = SWZ ? ((lane >> 2) & 1) * 2 : 0;            // element offset of this lane's first 16-byte half (SRow::ld_swz)
         // folded coefficients (the same in both code paths below, so a cell's value does not depend on which tile - plain or
         // special - computed it: redundant halo copies stay bit-identical to the owner's value)
         const double q4 = 0.25 * nscale, axd = ax * dinv, ayd = ay * dinv, nsd = nscale * dinv;
@@ -285,10 +316,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
             constexpr int SENT = 0x7ff00000;                        // high word of +Inf.  The sentinels are +Inf and the positive quiet NaN, so a
             // SIGNED compare of the high word tells them from every finite value (negative values are negative integers)
             double r[SPL] = {0.0, 0.0, 0.0, 0.0};
-            if (MODE == 0 || !STREAM_RB_LDS64) SRow<T>::ld(rhs_row, r);
+            if (MODE == 0 || !STREAM_RB_LDS64) SRow<T>::ld_swz(rhs_row, swz, r);
             const int act = k < nact;                               // warp-uniform (always true unless VAR == 2)
             if (MODE == 0) {
-#if STREAM_LATE_SHFL
+#if !STREAM_EARLY_SHFL_J
                 const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
 #else
                 const double Wn = NbW[k], En = NbE[k];             // neighbours of C, shuffled during the previous row step
@@ -320,7 +351,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 const bool even_cells = (((PB + jrow) % 2 + 2) % 2) == want;       // compile time
                 const int rown = row >= r0 && row < r1;
                 // this row step uses the west neighbour (cells 0, 2) or the east one (cells 1, 3); the next one the other
-#if STREAM_LATE_SHFL
+#if !STREAM_EARLY_SHFL_RB
                 const double Wn = __shfl_up_sync(FULLM, C[3], 1), En = __shfl_down_sync(FULLM, C[0], 1);
 #else
                 const double Wn = NbW[k], En = NbE[k];
@@ -328,8 +359,8 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 else NbW[k] = __shfl_up_sync(FULLM, N[3], 1);
 #endif
                 if (STREAM_RB_LDS64) {
-                    if (even_cells) { r[0] = (double)rhs_row[0]; r[2] = (double)rhs_row[2]; }
-                    else { r[1] = (double)rhs_row[1]; r[3] = (double)rhs_row[3]; }
+                    if (even_cells) { r[0] = (double)rhs_row[0 ^ swz]; r[2] = (double)rhs_row[2 ^ swz]; }
+                    else { r[1] = (double)rhs_row[1 ^ swz]; r[3] = (double)rhs_row[3 ^ swz]; }
                 }
                 auto cell = [&](int m, double e, double w) {
                     const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
@@ -362,7 +393,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
             mbar_wait(&bars[slot], (uint32_t)((k / NS) & 1));
             const T* sp = ring_p + slot * ARR + SPL * lane;
             const int q = q0 + SKR * k;
-            T* sg = stage + (nstore & 1) * ARR;
+            T* sg = stage + (NSTG == 2 ? (nstore & 1) : 0) * ARR;
             // rhs rows of the chunks k, k-1, ... (this lane's columns): the level that computes row q + j - 1 - lv reads
             // row (j - 1 - lv) mod 3 of chunk k + floor((j - 1 - lv) / 3), all compile-time offsets
             const T* rb[KEEP + 2];
@@ -373,7 +404,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
             }
             const int orow = q - L;                                  // first row leaving the pipeline in this chunk
             const bool do_store = orow >= r0 && orow < r1;          // whole chunks by construction
-            if (do_store && nstore >= 2) {                           // the staging buffer's previous TMA store has read it
+            if (NSTG == 2 && do_store && nstore >= 2) {              // the staging buffer's previous TMA store has read it
                 if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
             }
@@ -381,7 +412,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < SKR; ++j) {
                     // ring row j of this slot = phi row q + j enters level 1 as its north row
-                    SRow<T>::ld(sp + j * SW, R[0][(j + 2) % 3]);
+                    SRow<T>::ld_swz(sp + j * SW, swz, R[0][(j + 2) % 3]);
 #pragma unroll
                     for (int lv = 0; lv < L; ++lv) {
                         const int row = q + j - 1 - lv;                  // row computed by level lv + 1
@@ -395,6 +426,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                         } else {
                             double out[SPL];
                             level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
+                            if (NSTG == 1 && j == 0 && do_store && nstore >= 1) {   // single buffer: the previous chunk's store has read it
+                                if (lane == 0) tma_store_wait_read<0>();             // (issued a third of a chunk ago)
+                                __syncwarp();
+                            }
                             if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
                         }
                     }
@@ -564,13 +599,15 @@ template <typename T, int MODE, int L, int NS, bool SOR, bool CHECK>
 static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
                          unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* cflags, const StreamTile* tiles, cudaStream_t s) {
     constexpr int KEEP = (L + SKR - 1) / SKR;
-    const size_t smem = (size_t)SWARPS * (NS + NS + KEEP + 2) * SKR * SW * sizeof(T) + SWARPS * NS * sizeof(uint64_t);
+    const size_t smem = (size_t)SWARPS * (NS + NS + KEEP + (STREAM_STAGE1 ? 1 : 2)) * SKR * SW * sizeof(T) + SWARPS * NS * sizeof(uint64_t);
     auto kern = k_poisson_stream<T, MODE, L, NS, SOR, CHECK>;
     static bool configured = false;
     if (!configured) {
         if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
             cudaGetLastError(); g_stream_err = "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)"; return -1;
         }
+        // STREAM_MINB blocks per SM only fit with the largest shared-memory carve-out
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared) != cudaSuccess) cudaGetLastError();
         configured = true;
     }
     const int ntile = P.ntile;
@@ -647,7 +684,7 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     P.n_strips = (g.nx + P.OW - 1) / P.OW;
     // tiles: every tile resident at once (one warp per tile), 8 warps per SM; the plan kernel below cuts the strips into
     // ntile row ranges of equal cost (at least 4 groups of 3 rows each)
-    const int want = env_int("B200CFD_STREAM_WARPS_PER_SM", 8) * n_sm;
+    const int want = env_int("B200CFD_STREAM_WARPS_PER_SM", SWARPS * STREAM_MINB) * n_sm;
     const int G = (g.ny + SKR - 1) / SKR, min_groups = 4;
     int per_strip_max = G / min_groups;                            // (the plan's own cap, which knows alpha, is tighter)
     if (per_strip_max < 1) per_strip_max = 1;
@@ -705,8 +742,11 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
     ps->rhs_src = div; ps->mask_src = mask; ps->rhs_ny = g.ny; ps->rhs_nx = g.nx; ps->rhs_L = L; ps->rhs_dtype = dtype;
     ps->plan_ntile = P.ntile; ps->plan_alpha = alpha;
     CUtensorMap m_phi, m_alt, m_rhs, o_phi, o_alt;
-    if (!tma_make_2d(&m_phi, dtype, phi, g.nx, g.ny, g.pitch, SW, SKR) || !tma_make_2d(&m_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, SW, SKR) ||
-        !tma_make_2d(&m_rhs, dtype, ps->rhs_s, g.nx, g.ny, g.pitch, SW, SKR) ||
+    const bool swz = STREAM_SWZ && dtype == 0;                      // fp64 rows land swizzled (tma_make_3d_swz32)
+    auto make_in = [&](CUtensorMap* m, const void* base) {
+        return swz ? tma_make_3d_swz32(m, base, g.nx, g.ny, g.pitch, SW, SKR) : tma_make_2d(m, dtype, base, g.nx, g.ny, g.pitch, SW, SKR);
+    };
+    if (!make_in(&m_phi, phi) || !make_in(&m_alt, ps->alt) || !make_in(&m_rhs, ps->rhs_s) ||
         !tma_make_2d(&o_phi, dtype, phi, g.nx, g.ny, g.pitch, P.OW, SKR) || !tma_make_2d(&o_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, P.OW, SKR)) {
         g_stream_err = "cuTensorMapEncodeTiled failed"; return -1;
     }

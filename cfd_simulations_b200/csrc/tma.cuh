@@ -33,6 +33,11 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  ::"r"(smem_u32(dst)), "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar)) : "memory");
 }
+// the same for a 3-D map (tma_make_3d_swz32: coordinates (0, x / 4, y))
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
 // shared -> global, 2-D box; elements outside the tensor are not written.  Bulk-group completion.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int x, int y, const void* src) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];"
@@ -66,6 +71,23 @@ inline bool tma_make_2d(CUtensorMap* m, int dtype, const void* base, int nx, int
     return enc(m, dtype == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
                strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// The same fp64 field seen as (ny, nx / 4, 4): 32-byte units of 4 doubles, so that the box rows can be written to shared
+// memory with the 32-byte swizzle (the swizzle modes need an inner box extent no larger than their span).  The box holds
+// the same bytes in the same order as tma_make_2d's, except that inside every odd 128-byte line the two 16-byte halves of each
+// 32-byte unit are exchanged (byte-address bit 4 ^= bit 7; the destination must be 256-byte aligned).  A warp whose lane l
+// reads the 32-byte unit l of a row with two 128-bit loads then hits every bank once per quarter-warp; unswizzled, lanes l
+// and l + 4 collide and each load takes twice the shared-memory cycles.  nx and box_w must be multiples of 4.
+inline bool tma_make_3d_swz32(CUtensorMap* m, const void* base, int nx, int ny, long long pitch, int box_w, int box_h) {
+    PFN_cuTensorMapEncodeTiled_v12000 enc = tma_encoder();
+    if (!enc || nx % 4 || box_w % 4) return false;
+    cuuint64_t dims[3] = {4, (cuuint64_t)(nx / 4), (cuuint64_t)ny};
+    cuuint64_t strides[2] = {32, (cuuint64_t)(pitch * 8)};
+    cuuint32_t box[3] = {4, (cuuint32_t)(box_w / 4), (cuuint32_t)box_h};
+    cuuint32_t estr[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 }  // namespace b200cfd

@@ -617,7 +617,9 @@ static int stream_launch(const CUtensorMap& mi, const CUtensorMap& mr, const CUt
 }
 
 // pipeline depths instantiated: 2 and 6 levels (a shallower pass runs in the deeper pipeline with inactive levels)
+#ifndef STREAM_NS
 #define STREAM_NS 2
+#endif
 template <typename T, int MODE, bool SOR, bool CHECK>
 static int stream_depth(int L, const CUtensorMap& mi, const CUtensorMap& mr, const CUtensorMap& mo, const StreamParams& P,
                         unsigned long long* slots, StreamCtl* ctl, int role, int pass_index, const uint8_t* cflags, const StreamTile* tiles, cudaStream_t s) {
@@ -716,8 +718,11 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         if (cudaMalloc(&ps->plan_i, plan_ints * sizeof(int)) != cudaSuccess) { cudaGetLastError(); g_stream_err = "cudaMalloc(plan scratch)"; return -1; }
         ps->plan_cap = plan_ints;
     }
-    // extra cost of a chunk with class selects, percent of a plain chunk (instruction counts of the two chunk bodies: 1.39 / 1.25)
-    int alpha = env_int("B200CFD_STREAM_ALPHA", mode == 0 ? 35 : 20);
+    // extra cost of a chunk with class selects, percent of a plain chunk.  Measured, not derived from instruction counts (the
+    // select body has 1.4 x the instructions): at 8192^2 Jacobi gives 814 / 867 / 924 GLUPS at 0 / 35 / 50 before the swizzle
+    // and 1091 / 1211 / 1217 / 1139 at 50 / 100 / 150 / 250 after it; red-black is flat from 35 to 150
+    // (profiles/r04b_alpha.txt, r04d_alpha.txt, r04e_alpha.txt; tools/alpha_sweep.py)
+    int alpha = env_int("B200CFD_STREAM_ALPHA", 100);
     if (alpha < 0) alpha = 0;
     if (alpha > 400) alpha = 400;
     const bool reuse = ps->keep_rhs && ps->rhs_src == div && ps->mask_src == (const void*)mask && ps->rhs_ny == g.ny &&

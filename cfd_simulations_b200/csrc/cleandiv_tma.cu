@@ -24,20 +24,11 @@ namespace b200cfd {
 #define TPL 4         // columns per lane
 #define TWARPS 4      // warps (tiles) per block
 #define TKR 3         // rows per ring slot = unroll of the row loop = rotation period of the register rows
-#ifndef CLEAN_SWZ
-#define CLEAN_SWZ 1   // fp64: rows land in shared memory with TMA's 32-byte swizzle (tma_make_3d_swz32): the 128-bit row loads of
-#endif                // lane l and lane l + 4 otherwise hit the same banks (2-way conflict on every load; found on poisson_stream.cu)
 
 template <typename T> struct Sm4;
 template <> struct Sm4<double> {
     static __device__ __forceinline__ void ld(const double* p, double (&o)[TPL]) {
         const double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
-        o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
-    }
-    // row written by a swizzled TMA box: sw = 2 for the lanes whose 32-byte unit lies in an odd 128-byte line (lane bit 2),
-    // where the unit's two 16-byte halves are exchanged; 0 otherwise
-    static __device__ __forceinline__ void ld_swz(const double* p, int sw, double (&o)[TPL]) {
-        const double2 a = *reinterpret_cast<const double2*>(p + sw), b = *reinterpret_cast<const double2*>(p + 2 - sw);
         o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
     }
     static __device__ __forceinline__ void st(double* p, const double (&x)[TPL]) {
@@ -50,7 +41,6 @@ template <> struct Sm4<float> {
         const float4 t = *reinterpret_cast<const float4*>(p);
         o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
     }
-    static __device__ __forceinline__ void ld_swz(const float* p, int, double (&o)[TPL]) { ld(p, o); }
     static __device__ __forceinline__ void st(float* p, const double (&x)[TPL]) {
         *reinterpret_cast<float4*>(p) = make_float4((float)x[0], (float)x[1], (float)x[2], (float)x[3]);
     }
@@ -71,8 +61,7 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
     constexpr int DV = MODE == 2 ? 1 : 0;
     constexpr int ARR = TKR * TW;                  // elements per array per slot
     constexpr int SLOT = NARR * ARR;
-    extern __shared__ __align__(1024) unsigned char smem_raw[];
-    constexpr bool SWZ = CLEAN_SWZ && sizeof(T) == 8;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
     pdl_wait(); pdl_trigger();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int tile = blockIdx.x * TWARPS + warp;
@@ -96,22 +85,15 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
     const int q0 = iw0 + RA - WUC * TKR;                       // first ingest row (may be negative: zero fill)
     const int jw0 = js - cp.apron_h;                           // window origin, a multiple of 4 (may be negative)
     const int c0 = jw0 + TPL * lane;
-    const int swz = SWZ ? ((lane >> 2) & 1) * 2 : 0;           // element offset of this lane's first 16-byte half (Sm4::ld_swz)
 
     auto issue = [&](int k) {                                  // lane 0: TMA boxes of chunk k into its slot
         const int slot = k % NSLOT;
         T* dst = ring + slot * SLOT;
         const int qk = q0 + TKR * k;
         mbar_expect_tx(&bars[slot], (uint32_t)(SLOT * sizeof(T)));
-        if (SWZ) {                                             // 3-D swizzled view: (0, x / 4, y); jw0 is a multiple of 4
-            tma_load_3d(dst, &tm_u, 0, jw0 / 4, qk - DU, &bars[slot]);
-            tma_load_3d(dst + ARR, &tm_v, 0, jw0 / 4, qk - DV, &bars[slot]);
-            if (NARR == 3) tma_load_3d(dst + 2 * ARR, &tm_p, 0, jw0 / 4, qk, &bars[slot]);
-        } else {
-            tma_load_2d(dst, &tm_u, jw0, qk - DU, &bars[slot]);
-            tma_load_2d(dst + ARR, &tm_v, jw0, qk - DV, &bars[slot]);
-            if (NARR == 3) tma_load_2d(dst + 2 * ARR, &tm_p, jw0, qk, &bars[slot]);
-        }
+        tma_load_2d(dst, &tm_u, jw0, qk - DU, &bars[slot]);
+        tma_load_2d(dst + ARR, &tm_v, jw0, qk - DV, &bars[slot]);
+        if (NARR == 3) tma_load_2d(dst + 2 * ARR, &tm_p, jw0, qk, &bars[slot]);
     };
     if (lane == 0) {
         const int n0 = NCH < NSLOT ? NCH : NSLOT;
@@ -188,9 +170,9 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
         constexpr bool COMPUTE = decltype(compute_tag)::value;
         (void)V1;
         double uq[TPL], sv[TPL];
-        Sm4<T>::ld_swz(sp, swz, uq);
+        Sm4<T>::ld(sp, uq);
         if (MODE == 0) {
-            Sm4<T>::ld_swz(sp + ARR, swz, V2);
+            Sm4<T>::ld(sp + ARR, V2);
             if (COMPUTE) {
                 const double uW = __shfl_up_sync(FULLM, uq[3], 1), uE = __shfl_down_sync(FULLM, uq[0], 1);
 #pragma unroll
@@ -201,8 +183,8 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
                 }
             }
         } else if (MODE == 1) {
-            Sm4<T>::ld_swz(sp + ARR, swz, V2);
-            Sm4<T>::ld_swz(sp + 2 * ARR, swz, P1);
+            Sm4<T>::ld(sp + ARR, V2);
+            Sm4<T>::ld(sp + 2 * ARR, P1);
             if (COMPUTE) {
                 const double uW = __shfl_up_sync(FULLM, uq[3], 1), uE = __shfl_down_sync(FULLM, uq[0], 1);
                 const double pE3 = __shfl_down_sync(FULLM, P0[0], 1);
@@ -216,8 +198,8 @@ k_clean_sweep_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constan
             }
         } else {
             double vq[TPL];
-            Sm4<T>::ld_swz(sp + ARR, swz, vq);
-            Sm4<T>::ld_swz(sp + 2 * ARR, swz, P2);
+            Sm4<T>::ld(sp + ARR, vq);
+            Sm4<T>::ld(sp + 2 * ARR, P2);
             // corrected v of row q-1 = i+1 (the correction touches interior cells only, v5.py:254-256)
             const double vin = ((q - 1 >= 1) && (q - 1 < g.ny - 1)) ? 1.0 : 0.0;        // warp-uniform
 #pragma unroll
@@ -348,11 +330,9 @@ bool launch_clean_sweep_tma(int dtype, const Geom& g, const CleanPlan& cp, const
                             void* psi_new, int mode, cudaStream_t s) {
     if (!clean_sweep_tma_ok(dtype, g, cp, u, v, psi_old, psi_new)) return false;
     CUtensorMap mu, mv, mp;
-    const bool swz = CLEAN_SWZ && dtype == 0;                  // fp64 rows land swizzled (clean_sweep_tma_ok: nx and the window origin are multiples of 4)
-    auto make = [&](CUtensorMap* m, const void* base) {
-        return swz ? tma_make_3d_swz32(m, base, g.nx, g.ny, g.pitch, TW, TKR) : tma_make_2d(m, dtype, base, g.nx, g.ny, g.pitch, TW, TKR);
-    };
-    if (!make(&mu, u) || !make(&mv, v) || !make(&mp, mode ? psi_old : u)) return false;
+    if (!tma_make_2d(&mu, dtype, u, g.nx, g.ny, g.pitch, TW, TKR) || !tma_make_2d(&mv, dtype, v, g.nx, g.ny, g.pitch, TW, TKR) ||
+        !tma_make_2d(&mp, dtype, mode ? psi_old : u, g.nx, g.ny, g.pitch, TW, TKR))
+        return false;
     const int ntile = cp.n_strips * cp.n_tiles;
     const int nblk = (ntile + TWARPS - 1) / TWARPS;
     if (nblk <= 0) return true;

@@ -40,8 +40,9 @@ namespace b200cfd {
 #define SKR 3         // rows per ring slot = unroll of the row loop
 #define FULLM 0xffffffffu
 // A/B switches (tools/build_variant.sh): shuffle the north row one row step early (see NbW / NbE) instead of the centre row
-// at the point of use, per mode.  Measured at 8192^2 (profiles/r04b_alpha.txt, r04e_alpha.txt): early shuffles cost Jacobi
-// 1-4 % (8 more registers) and gain red-black 4-10 %.
+// at the point of use, per mode; red-black levels load only the two rhs values they use (two LDS.64) instead of the whole
+// 4-cell row.  Measured at 8192^2 (profiles/r04b_alpha.txt): early shuffles cost Jacobi 4 % (964 -> 924 GLUPS, 8 more
+// registers) and gain SOR 4 % (461 -> 480); LDS.64 is within the noise (+2 % SOR, -1 % GS).
 #ifndef STREAM_EARLY_SHFL_J
 #define STREAM_EARLY_SHFL_J 0
 #endif
@@ -53,6 +54,9 @@ namespace b200cfd {
 #endif
 #ifndef STREAM_SWZ
 #define STREAM_SWZ 1      // fp64: phi and rhs rows land in shared memory with TMA's 32-byte swizzle (conflict-free 128-bit row loads)
+#endif
+#ifndef STREAM_RB_LDS64
+#define STREAM_RB_LDS64 0
 #endif
 
 struct StreamCtl {            // device-resident control of a tolerance-terminated solve
@@ -286,11 +290,6 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         double NbW[L], NbE[L];
 #pragma unroll
         for (int k = 0; k < L; ++k) { NbW[k] = 0.0; NbE[k] = 0.0; }
-        double Rk[(L + 1) / 2][SPL];                               // rhs rows the even levels loaded in the previous row step (see body)
-#pragma unroll
-        for (int h = 0; h < (L + 1) / 2; ++h)
-#pragma unroll
-            for (int m = 0; m < SPL; ++m) Rk[h][m] = 0.0;
 
         const int scol = SPL * lane - P.H;                          // this lane's first column inside the staged (owned) row
         const bool st_lane = scol >= 0 && scol + SPL <= P.OW;
@@ -311,11 +310,13 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
         // one level: row `row` of sweep k+1 from rows S (row-1), C (row), N (row+1) of sweep k and the rhs of `row`.
         // Straight-line code: the shuffles (of the NORTH row, for the next row step: see NbW / NbE) are unconditional.
         auto level = [&](auto pb_tag, auto var_tag, int k, int jrow, int row, const double (&S)[SPL], const double (&C)[SPL],
-                         const double (&N)[SPL], const double (&r)[SPL], double (&out)[SPL]) {
+                         const double (&N)[SPL], const T* rhs_row, double (&out)[SPL]) {
             constexpr int PB = decltype(pb_tag)::value;
             constexpr int VAR = decltype(var_tag)::value;
             constexpr int SENT = 0x7ff00000;                        // high word of +Inf.  The sentinels are +Inf and the positive quiet NaN, so a
             // SIGNED compare of the high word tells them from every finite value (negative values are negative integers)
+            double r[SPL] = {0.0, 0.0, 0.0, 0.0};
+            if (MODE == 0 || !STREAM_RB_LDS64) SRow<T>::ld_swz(rhs_row, swz, r);
             const int act = k < nact;                               // warp-uniform (always true unless VAR == 2)
             if (MODE == 0) {
 #if !STREAM_EARLY_SHFL_J
@@ -357,6 +358,10 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 if (even_cells) NbE[k] = __shfl_down_sync(FULLM, N[0], 1);
                 else NbW[k] = __shfl_up_sync(FULLM, N[3], 1);
 #endif
+                if (STREAM_RB_LDS64) {
+                    if (even_cells) { r[0] = (double)rhs_row[0 ^ swz]; r[2] = (double)rhs_row[2 ^ swz]; }
+                    else { r[1] = (double)rhs_row[1 ^ swz]; r[3] = (double)rhs_row[3 ^ swz]; }
+                }
                 auto cell = [&](int m, double e, double w) {
                     const double t = fma(ayd, N[m] + S[m], nsd * r[m]);
                     double pn = fma(axd, e + w, t);
@@ -408,26 +413,19 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 for (int j = 0; j < SKR; ++j) {
                     // ring row j of this slot = phi row q + j enters level 1 as its north row
                     SRow<T>::ld_swz(sp + j * SW, swz, R[0][(j + 2) % 3]);
-                    // rhs: level lv + 1 (lv even) reads the row whose rhs level lv + 2 reads one row step later, so every rhs
-                    // row is loaded ONCE per pair of levels and kept for one row step (Rk): half the shared-memory loads.  A
-                    // red-black pair uses complementary cells of the row (the two colours), so the full 128-bit loads, which
-                    // the swizzle makes conflict-free, have no idle half either.
-                    double rnew[(L + 1) / 2][SPL];
 #pragma unroll
                     for (int lv = 0; lv < L; ++lv) {
                         const int row = q + j - 1 - lv;                  // row computed by level lv + 1
                         const int off = j - 1 - lv;                      // compile time after unrolling
                         const int back = off >= 0 ? 0 : (-off + SKR - 1) / SKR, jr = off + back * SKR;
-                        if (lv % 2 == 0) SRow<T>::ld_swz(rb[back] + jr * SW, swz, rnew[lv / 2]);
-                        const double (&r)[SPL] = (lv % 2 == 0) ? rnew[lv / 2] : Rk[lv / 2];
                         if (lv + 1 < L) {
                             // the level writes straight into the next level's north row (no copy: the ncu source page
                             // of the first version showed a quarter of the issue slots going to register moves)
-                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], r,
+                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW,
                                   R[lv + 1 < L ? lv + 1 : lv][(j + 2) % 3]);
                         } else {
                             double out[SPL];
-                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], r, out);
+                            level(pb_tag, var_tag, lv, off, row, R[lv][j % 3], R[lv][(j + 1) % 3], R[lv][(j + 2) % 3], rb[back] + jr * SW, out);
                             if (NSTG == 1 && j == 0 && do_store && nstore >= 1) {   // single buffer: the previous chunk's store has read it
                                 if (lane == 0) tma_store_wait_read<0>();             // (issued a third of a chunk ago)
                                 __syncwarp();
@@ -435,10 +433,6 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                             if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
                         }
                     }
-#pragma unroll
-                    for (int h = 0; h < (L + 1) / 2; ++h)
-#pragma unroll
-                        for (int m = 0; m < SPL; ++m) Rk[h][m] = rnew[h][m];
                 }
             };
             auto variants = [&](auto pb_tag) {

@@ -20,7 +20,7 @@ PL="python bench.py --steps 2 --warmup 3 --no-cpu --no-scaling-base --no-poisson
 $PL > $o/plain_step_large.log 2>&1 && timeout 600 ncu --set full --clock-control none -k regex:"k_(predictor|div_rb1|clean|finalize|ctl)" \
   --launch-skip 18 --launch-count 6 -f -o $o/prof_${tag}_step16384 $PL > $o/ncu_step_large.log 2>&1; echo "ncu step 16384 rc=$?"
 Q="python bench_poisson.py --no-cpu --sweeps 24 --depths 1,0"
-$Q > $o/plain_poisson.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_(poisson_stream|stream_make_rhs)" \
+$Q > $o/plain_poisson.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_(poisson_stream|stream_make_rhs|stream_plan)" \
   --launch-skip 2 --launch-count 14 -f -o $o/prof_${tag}_poisson_stream $Q > $o/ncu_ps.log 2>&1; echo "ncu poisson stream rc=$?"
 timeout 600 ncu --set full --clock-control none -k regex:"k_(jacobi|rbgs_color)" --launch-skip 46 --launch-count 6 -f -o $o/prof_${tag}_poisson_1sweep $Q > $o/ncu_p1.log 2>&1; echo "ncu poisson one-sweep rc=$?"
 QT="env B200CFD_POISSON_STREAM=0 python bench_poisson.py --no-cpu --sweeps 24 --depths 0"

@@ -52,6 +52,12 @@ namespace b200cfd {
 #ifndef STREAM_STAGE1
 #define STREAM_STAGE1 0   // one staging buffer for the output rows instead of two (3 KB less shared memory per warp)
 #endif
+#ifndef STREAM_ST_SWZ
+#define STREAM_ST_SWZ 0   // fp64: the staged output rows are written swizzled too and stored through a swizzled 3-D map
+#endif
+#ifndef STREAM_PLAN_STRIP_MAJOR
+#define STREAM_PLAN_STRIP_MAJOR 0   // tile table ordered strip by strip instead of row-major over (tile-in-strip, strip)
+#endif
 #ifndef STREAM_SWZ
 #define STREAM_SWZ 1      // fp64: phi and rhs rows land in shared memory with TMA's 32-byte swizzle (conflict-free 128-bit row loads)
 #endif
@@ -99,6 +105,10 @@ template <> struct SRow<double> {
         *reinterpret_cast<double2*>(p) = make_double2(x[0], x[1]);
         *reinterpret_cast<double2*>(p + 2) = make_double2(x[2], x[3]);
     }
+    static __device__ __forceinline__ void st_swz(double* p, int sw, const double (&x)[SPL]) {
+        *reinterpret_cast<double2*>(p + sw) = make_double2(x[0], x[1]);
+        *reinterpret_cast<double2*>(p + 2 - sw) = make_double2(x[2], x[3]);
+    }
 };
 template <> struct SRow<float> {
     static __device__ __forceinline__ void ld(const float* p, double (&o)[SPL]) {
@@ -106,6 +116,7 @@ template <> struct SRow<float> {
         o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
     }
     static __device__ __forceinline__ void ld_swz(const float* p, int, double (&o)[SPL]) { ld(p, o); }   // (one 128-bit load per lane: no conflicts)
+    static __device__ __forceinline__ void st_swz(float* p, int, const double (&x)[SPL]) { st(p, x); }
     static __device__ __forceinline__ void st(float* p, const double (&x)[SPL]) {
         *reinterpret_cast<float4*>(p) = make_float4((float)x[0], (float)x[1], (float)x[2], (float)x[3]);
     }
@@ -199,6 +210,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
     constexpr int NSR = NS + KEEP;                // rhs ring: NS slots of lead + the ones the pipeline still reads
     constexpr int NSTG = STREAM_STAGE1 ? 1 : 2;
     constexpr bool SWZ = STREAM_SWZ && sizeof(T) == 8;
+    constexpr bool STSWZ = STREAM_ST_SWZ && sizeof(T) == 8;
     constexpr int WARP_ELEMS = (NS + NSR + NSTG) * ARR;   // phi ring, rhs ring, staging buffers of 3 output rows
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     int nact = P.nact;
@@ -293,6 +305,11 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
 
         const int scol = SPL * lane - P.H;                          // this lane's first column inside the staged (owned) row
         const bool st_lane = scol >= 0 && scol + SPL <= P.OW;
+        // swizzled staging (STSWZ): row j of the dense OW-column box starts at byte 8 OW j of a 256-byte aligned buffer; this
+        // lane's 32-byte unit has its halves exchanged when bit 7 of its byte offset is set
+        int stsw[SKR];
+#pragma unroll
+        for (int j = 0; j < SKR; ++j) stsw[j] = (STSWZ && st_lane) ? (((8 * P.OW * j + 8 * scol) >> 7) & 1) * 2 : 0;
         const T* ring_rl = ring_r + SPL * lane;
         const int swz = SWZ ? ((lane >> 2) & 1) * 2 : 0;            // element offset of this lane's first 16-byte half (SRow::ld_swz)
         // folded coefficients (the same in both code paths below, so a cell's value does not depend on which tile - plain or
@@ -430,7 +447,7 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                                 if (lane == 0) tma_store_wait_read<0>();             // (issued a third of a chunk ago)
                                 __syncwarp();
                             }
-                            if (do_store && st_lane) SRow<T>::st(sg + j * P.OW + scol, out);
+                            if (do_store && st_lane) SRow<T>::st_swz(sg + j * P.OW + scol, stsw[j], out);
                         }
                     }
                 }
@@ -447,7 +464,8 @@ k_poisson_stream(const __grid_constant__ CUtensorMap tm_in, const __grid_constan
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    tma_store_2d(&tm_out, x0, orow, sg);             // 3 dense rows of the OW owned columns
+                    if (STSWZ) tma_store_3d(&tm_out, 0, x0 / 4, orow, sg);
+                    else tma_store_2d(&tm_out, x0, orow, sg);        // 3 dense rows of the OW owned columns
                     tma_store_commit();
                 }
                 ++nstore;
@@ -549,7 +567,12 @@ k_stream_plan(StreamPlanArgs a, int* __restrict__ seg, int* __restrict__ cost, i
             t.s = s; t.pad = 0;
             t.r0 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j);
             t.r1 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j + 1);
-            if (first[s] + j < a.ntile) tiles[first[s] + j] = t;
+#if STREAM_PLAN_STRIP_MAJOR
+            const int idx = first[s] + j;
+#else
+            const int idx = plan_tile_index(n, a.n_strips, s, j);
+#endif
+            if (idx < a.ntile) tiles[idx] = t;
         }
 }
 
@@ -752,7 +775,8 @@ int poisson_stream_run(PoissonStream** pps, int dtype, int mode, const Geom& g, 
         return swz ? tma_make_3d_swz32(m, base, g.nx, g.ny, g.pitch, SW, SKR) : tma_make_2d(m, dtype, base, g.nx, g.ny, g.pitch, SW, SKR);
     };
     if (!make_in(&m_phi, phi) || !make_in(&m_alt, ps->alt) || !make_in(&m_rhs, ps->rhs_s) ||
-        !tma_make_2d(&o_phi, dtype, phi, g.nx, g.ny, g.pitch, P.OW, SKR) || !tma_make_2d(&o_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, P.OW, SKR)) {
+        !((STREAM_ST_SWZ && dtype == 0) ? tma_make_3d_swz32(&o_phi, phi, g.nx, g.ny, g.pitch, P.OW, SKR) : tma_make_2d(&o_phi, dtype, phi, g.nx, g.ny, g.pitch, P.OW, SKR)) ||
+        !((STREAM_ST_SWZ && dtype == 0) ? tma_make_3d_swz32(&o_alt, ps->alt, g.nx, g.ny, g.pitch, P.OW, SKR) : tma_make_2d(&o_alt, dtype, ps->alt, g.nx, g.ny, g.pitch, P.OW, SKR))) {
         g_stream_err = "cuTensorMapEncodeTiled failed"; return -1;
     }
     const bool check = tol > 0.0 && mode == 1;
@@ -839,7 +863,11 @@ extern "C" int b200cfd_stream_plan_host(const uint8_t* cflags, int n_strips, int
     for (int s = 0; s < n_strips; ++s) { n[s] = plan_tiles_at(cost[s], lo, cap); first[s] = f; f += n[s]; }
     for (int s = 0; s < n_strips; ++s)
         for (int j = 0; j < n[s]; ++j) {
+#if STREAM_PLAN_STRIP_MAJOR
             StreamTile& d = t[first[s] + j];
+#else
+            StreamTile& d = t[plan_tile_index(n, n_strips, s, j)];
+#endif
             d.s = s; d.pad = 0;
             d.r0 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j);
             d.r1 = plan_cut_row(a, s, seg + (size_t)s * nseg, cost[s], n[s], j + 1);

@@ -97,4 +97,15 @@ PLAN_HD inline int plan_cut_row(const StreamPlanArgs& a, int s, const int* pre, 
     return row;
 }
 
+// item (strip, tile j): position of the tile in the table.  Row-major over (j, strip): the j-th tiles of all strips are
+// neighbours in the table, so the 4 warps of a block (4 consecutive entries) and the blocks next to it work on ADJACENT strips
+// at (nearly) the same rows, and what the machine reads at any moment is runs of neighbouring 1 KB row segments rather
+// than 1184 unrelated ones (strips of equal cost have identical cuts).  n[] = tiles per strip.
+PLAN_HD inline int plan_tile_index(const int* n, int n_strips, int s, int j) {
+    int idx = 0;
+    for (int t = 0; t < n_strips; ++t) idx += n[t] < j ? n[t] : j;        // tiles 0 .. j-1 of every strip
+    for (int t = 0; t < s; ++t) idx += n[t] > j ? 1 : 0;                  // tile j of the strips before s
+    return idx;
+}
+
 }  // namespace b200cfd

@@ -121,6 +121,9 @@ def test_plan_8192_square_is_a_balanced_partition(alpha):
     n_s = np.array([np.sum(live[:, 0] == s) for s in range(n_strips)])
     T = (strip_cost / n_s).max()
     assert np.ceil(strip_cost / (T * 0.999)).sum() > ntile - n_strips
+    # table order: row-major over (tile-in-strip, strip): the first n_strips entries are the first tiles of strips 0, 1, 2, ...
+    assert np.array_equal(tiles[:n_strips, 0], np.arange(n_strips)) and np.all(tiles[:n_strips, 1] == 0)
+    assert np.all(tiles[len(live):, 2] == 0)                      # unused entries trail
     if alpha == 0:          # no cost difference: equal row ranges (to within one group)
         h = live[:, 2] - live[:, 1]
         assert h.max() - h.min() <= 6

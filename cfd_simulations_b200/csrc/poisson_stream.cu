@@ -3,8 +3,9 @@
 // omega != 1 gives SOR, the converged-solution counterpart of v2.py:284-306).
 //
 // One warp owns a 128-column window (4 columns per lane) and streams DOWN a chunk of rows.  Rows of phi and of the
-// right-hand side arrive through a per-warp ring of TMA boxes (cp.async.bulk.tensor.2d + mbarrier, 3 rows per slot,
-// several slots ahead, zero fill outside the array).  Each row then runs through a pipeline of L "levels" held in
+// right-hand side arrive through a per-warp ring of TMA boxes (cp.async.bulk.tensor + mbarrier, 3 rows per slot,
+// several slots ahead, zero fill outside the array; fp64 rows land with the 32-byte swizzle so that the lanes' 128-bit row
+// loads are free of bank conflicts, see STREAM_SWZ).  Each row then runs through a pipeline of L "levels" held in
 // registers: level k computes row q-k of sweep k from the rows q-k-1, q-k, q-k+1 of sweep k-1 (two of them kept in
 // registers, the third just produced), x-neighbours by warp shuffle, right-hand side of row q-k re-read from the ring.
 // Jacobi: one level per sweep; red-black: two levels (red half-sweep, black half-sweep) per iteration.  The row that
@@ -14,7 +15,10 @@
 // of poisson_tb.cu (4 shared-memory loads + 1 store per cell and sweep, 1.39 x staged area) depth costs almost nothing:
 // shared memory carries 8 B per cell and sweep (the right-hand side), everything else lives in registers.
 // Cell classes are data, not coordinates: k_stream_make_rhs folds the cylinder mask AND the non-updated border cells into
-// the right-hand side as sentinels (NaN = masked, +Inf = keep), so the kernel has no position tests at all.
+// the right-hand side as sentinels (NaN = masked, +Inf = keep), so the kernel has no position tests at all; the selects
+// that honour them run only in the 3-row chunks whose levels read one (per-chunk flags, also from k_stream_make_rhs).
+// Every tile is resident at once, so a pass lasts as long as its most expensive tile: the tiles come from a cost-balanced
+// plan built on the device from those flags (poisson_stream_plan.h, k_stream_plan).
 // Tolerance mode (red-black): per-iteration max|dphi| over the owned cells goes to its own slot (exact, order free); the
 // last block of a pass decides ON THE DEVICE whether the sequential algorithm would have stopped inside this pass
 // (v5.py:224-225) and, if so, with which depth the pass has to be redone from its intact input; every later launch
